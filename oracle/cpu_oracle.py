@@ -1,0 +1,147 @@
+"""TEST INFRASTRUCTURE ONLY — ctypes loader for the CPU oracles.
+
+  libcentrality_oracle.so        our restatement   (oracle/centrality_oracle.cpp)
+  _ref/libcugraph_ref_oracle.so  the reference's own host functions (oracle/ref_shim.cpp +
+                                 oracle/build_ref.sh), present when built in the container.
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs use it.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_PORT = os.path.join(_HERE, "libcentrality_oracle.so")
+_REF = os.path.join(_HERE, "_ref", "libcugraph_ref_oracle.so")
+_libs: dict[str, ctypes.CDLL] = {}
+
+
+def build(force: bool = False) -> None:
+    if force or not os.path.exists(_PORT) or (
+        os.path.getmtime(_PORT) < os.path.getmtime(os.path.join(_HERE, "centrality_oracle.cpp"))
+    ):
+        subprocess.check_call(["bash", os.path.join(_HERE, "build_ref.sh")])
+
+
+def port_lib() -> ctypes.CDLL:
+    if "port" not in _libs:
+        build()
+        _libs["port"] = ctypes.CDLL(_PORT)
+    return _libs["port"]
+
+
+def ref_available() -> bool:
+    return os.path.exists(_REF)
+
+
+def ref_lib() -> ctypes.CDLL:
+    if "ref" not in _libs:
+        _libs["ref"] = ctypes.CDLL(_REF)
+    return _libs["ref"]
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+def _sfx(dtype):
+    return {np.dtype(np.float32): "f32", np.dtype(np.float64): "f64"}[np.dtype(dtype)]
+
+
+def _prep(offsets, indices, weights, dtype):
+    offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+    indices = np.ascontiguousarray(indices, dtype=np.int32)
+    weights = None if weights is None else np.ascontiguousarray(weights, dtype=dtype)
+    return offsets, indices, weights
+
+
+def pagerank(offsets, indices, weights=None, *, dtype=np.float32, alpha=0.85, epsilon=1e-6,
+             max_iterations=500, personalization=None, initial_guess=None, fixed_iterations=0,
+             impl="port"):
+    """Returns (scores, iterations). impl="ref" runs the reference's own pagerank_reference."""
+    offsets, indices, weights = _prep(offsets, indices, weights, dtype)
+    nv = len(offsets) - 1
+    pr = np.zeros(nv, dtype=dtype) if initial_guess is None else np.array(initial_guess, dtype=dtype)
+    pv = pw = None
+    if personalization is not None:
+        pv = np.ascontiguousarray(personalization[0], dtype=np.int32)
+        pw = np.ascontiguousarray(personalization[1], dtype=dtype)
+    npers = 0 if pv is None else len(pv)
+    if impl == "ref":
+        fn = getattr(ref_lib(), "ref_pagerank_" + _sfx(dtype))
+        fn.restype = ctypes.c_long
+        rc = fn(_p(offsets), _p(indices), _p(weights), _p(pv), _p(pw), ctypes.c_int64(npers), _p(pr),
+                ctypes.c_int64(nv), ctypes.c_double(alpha), ctypes.c_double(epsilon),
+                ctypes.c_long(max_iterations), ctypes.c_int(initial_guess is not None))
+    else:
+        fn = getattr(port_lib(), "oracle_pagerank_" + _sfx(dtype))
+        fn.restype = ctypes.c_long
+        rc = fn(_p(offsets), _p(indices), _p(weights), _p(pv), _p(pw), ctypes.c_int64(npers), _p(pr),
+                ctypes.c_int64(nv), ctypes.c_double(alpha), ctypes.c_double(epsilon),
+                ctypes.c_long(max_iterations), ctypes.c_int(initial_guess is not None),
+                ctypes.c_long(fixed_iterations))
+    if rc < 0:
+        raise RuntimeError("PageRank failed to converge." if rc == -1 else "invalid input")
+    return pr, int(rc)
+
+
+def katz(offsets, indices, weights=None, *, dtype=np.float32, alpha=0.01, beta=1.0, betas=None,
+         epsilon=1e-6, max_iterations=500, initial_guess=None, normalize=False,
+         fixed_iterations=0, impl="port"):
+    offsets, indices, weights = _prep(offsets, indices, weights, dtype)
+    nv = len(offsets) - 1
+    kc = np.zeros(nv, dtype=dtype) if initial_guess is None else np.array(initial_guess, dtype=dtype)
+    b = None if betas is None else np.ascontiguousarray(betas, dtype=dtype)
+    if impl == "ref":
+        fn = getattr(ref_lib(), "ref_katz_" + _sfx(dtype))
+        fn.restype = ctypes.c_long
+        rc = fn(_p(offsets), _p(indices), _p(weights), _p(b), _p(kc), ctypes.c_int64(nv),
+                ctypes.c_double(alpha), ctypes.c_double(beta), ctypes.c_double(epsilon),
+                ctypes.c_long(max_iterations), ctypes.c_int(initial_guess is not None),
+                ctypes.c_int(normalize))
+    else:
+        fn = getattr(port_lib(), "oracle_katz_" + _sfx(dtype))
+        fn.restype = ctypes.c_long
+        rc = fn(_p(offsets), _p(indices), _p(weights), _p(b), _p(kc), ctypes.c_int64(nv),
+                ctypes.c_double(alpha), ctypes.c_double(beta), ctypes.c_double(epsilon),
+                ctypes.c_long(max_iterations), ctypes.c_int(initial_guess is not None),
+                ctypes.c_int(normalize), ctypes.c_long(fixed_iterations))
+    if rc < 0:
+        raise RuntimeError("Katz Centrality failed to converge.")
+    return kc, int(rc)
+
+
+def eigenvector(src, dst, weights=None, *, num_vertices, dtype=np.float32, epsilon=1e-6,
+                max_iterations=500, fixed_iterations=0, impl="port"):
+    """NB the reference oracle accumulates into tmp[src[e]] from old[dst[e]] (the test feeds it
+    the edge list in the orientation that makes this the pull direction)."""
+    src = np.ascontiguousarray(src, dtype=np.int32)
+    dst = np.ascontiguousarray(dst, dtype=np.int32)
+    w = None if weights is None else np.ascontiguousarray(weights, dtype=dtype)
+    out = np.zeros(num_vertices, dtype=dtype)
+    if impl == "ref":
+        fn = getattr(ref_lib(), "ref_eigenvector_" + _sfx(dtype))
+        fn.restype = ctypes.c_long
+        rc = fn(_p(src), _p(dst), _p(w), ctypes.c_int64(len(src)), _p(out),
+                ctypes.c_int64(num_vertices), ctypes.c_double(epsilon), ctypes.c_long(max_iterations))
+    else:
+        fn = getattr(port_lib(), "oracle_eigenvector_" + _sfx(dtype))
+        fn.restype = ctypes.c_long
+        rc = fn(_p(src), _p(dst), _p(w), ctypes.c_int64(len(src)), _p(out),
+                ctypes.c_int64(num_vertices), ctypes.c_double(epsilon), ctypes.c_long(max_iterations),
+                ctypes.c_long(fixed_iterations))
+    if rc < 0:
+        raise RuntimeError("Eigenvector Centrality failed to converge.")
+    return out, int(rc)
+
+
+def csc_from_coo(src, dst, weights, num_vertices):
+    """Un-renumbered CSC (rows = destinations) in input order, as the reference tests build the
+    host graph for pagerank_reference (pagerank_test.cpp:264-300)."""
+    order = np.argsort(dst, kind="stable")
+    offsets = np.zeros(num_vertices + 1, dtype=np.int64)
+    np.cumsum(np.bincount(dst, minlength=num_vertices), out=offsets[1:])
+    return offsets, np.asarray(src)[order].astype(np.int32), None if weights is None else np.asarray(weights)[order]
