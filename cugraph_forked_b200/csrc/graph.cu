@@ -1,0 +1,728 @@
+// Graph construction on the GPU: renumbering by descending major degree, degree segments,
+// COO -> CSC with ascending neighbours, out-weight sums, and the tile schedule of the pull
+// kernel.  B200-native replacement of
+//   cpp/src/structure/renumber_edgelist_impl.cuh:96-452 (compute_renumber_map), :923-994
+//   cpp/src/structure/detail/structure_utils.cuh:173-490 (compress_edgelist, sort_adjacency_list)
+//   cpp/src/structure/create_graph_from_edgelist_impl.cuh:570-774 (single-GPU path)
+//   cpp/src/structure/graph_view_impl.cuh:203-265 (degrees, weight sums)
+// Everything is hand-written kernels + the scan / radix sort of prims.cuh.  Instead of the
+// reference's atomic slot claim followed by a segmented neighbour sort, the CSC is produced
+// by ONE stable radix sort of (new_major << 32 | new_minor) keys, which yields the offsets
+// (from the already sorted degrees), the ascending neighbour lists and a deterministic weight
+// order at once.
+#include "graph.cuh"
+
+namespace b200 {
+
+namespace {
+
+constexpr int kThreads = 256;
+inline unsigned grid_for(size_t n, int per_thread = 1)
+{
+  size_t b = (n + size_t(kThreads) * per_thread - 1) / (size_t(kThreads) * per_thread);
+  if (b == 0) b = 1;
+  if (b > 0x7fffffffu) b = 0x7fffffffu;
+  return static_cast<unsigned>(b);
+}
+
+template <typename VT>
+__global__ void max_id_kernel(const VT* a, const VT* b, size_t n, unsigned long long* out,
+                              int* negative)
+{
+  unsigned long long m = 0;
+  int neg              = 0;
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    VT x = a[i];
+    if (x < 0) neg = 1;
+    else if (static_cast<unsigned long long>(x) > m) m = static_cast<unsigned long long>(x);
+    if (b) {
+      VT y = b[i];
+      if (y < 0) neg = 1;
+      else if (static_cast<unsigned long long>(y) > m) m = static_cast<unsigned long long>(y);
+    }
+  }
+  m = warp_max(m);
+  if ((threadIdx.x & 31) == 0) atomicMax(out, m);
+  if (neg) *negative = 1;
+}
+
+template <typename VT>
+__global__ void mark_present_kernel(const VT* a, const VT* b, size_t n, uint32_t* flags)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    flags[a[i]] = 1u;
+    if (b) flags[b[i]] = 1u;
+  }
+}
+
+// flags (0/1) + their exclusive scan -> compacted sorted vertex list
+template <typename VT>
+__global__ void compact_present_kernel(const uint32_t* flags, const uint32_t* pos, size_t n,
+                                       VT* sorted_vertices)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    if (flags[i]) sorted_vertices[pos[i]] = static_cast<VT>(i);
+  }
+}
+
+template <typename VT>
+__global__ void is_identity_kernel(const VT* v, size_t n, int* not_identity)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    if (v[i] != static_cast<VT>(i)) *not_identity = 1;
+  }
+}
+
+// position of an external id in the sorted unique vertex list
+template <typename VT>
+struct vertex_lookup {
+  int mode;  // 0: identity, 1: direct map (pos[id]), 2: binary search
+  const uint32_t* pos;
+  const VT* sorted;
+  int64_t n;
+  __device__ __forceinline__ int64_t operator()(VT id) const
+  {
+    if (mode == 0) return static_cast<int64_t>(id);
+    if (mode == 1) return static_cast<int64_t>(pos[id]);
+    int64_t lo = 0, hi = n;
+    while (lo < hi) {
+      int64_t mid = (lo + hi) >> 1;
+      if (sorted[mid] < id) lo = mid + 1;
+      else hi = mid;
+    }
+    return lo;
+  }
+};
+
+template <typename VT>
+__global__ void count_degree_kernel(const VT* majors, size_t n, vertex_lookup<VT> lk,
+                                    uint32_t* deg, int* bad)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    int64_t p = lk(majors[i]);
+    if (p < 0 || p >= lk.n || (lk.mode == 2 && lk.sorted[p] != majors[i])) { *bad = 1; continue; }
+    atomicAdd(&deg[p], 1u);
+  }
+}
+
+__global__ void max_u32_kernel(const uint32_t* a, size_t n, uint32_t* out)
+{
+  uint32_t m = 0;
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    m = max(m, a[i]);
+  m = warp_max(m);
+  if ((threadIdx.x & 31) == 0) atomicMax(out, m);
+}
+
+__global__ void degree_keys_kernel(const uint32_t* deg, size_t n, uint32_t maxdeg, uint32_t* keys,
+                                   uint32_t* vals)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    keys[i] = maxdeg - deg[i];  // ascending key == descending degree; LSD radix sort is stable
+    vals[i] = static_cast<uint32_t>(i);
+  }
+}
+
+template <typename VT>
+__global__ void finish_renumber_kernel(const uint32_t* sorted_keys, const uint32_t* sorted_vals,
+                                       size_t n, uint32_t maxdeg, const VT* sorted_vertices,
+                                       int identity, VT* labels, uint32_t* new_of_sorted,
+                                       uint32_t* sorted_deg)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    uint32_t v      = sorted_vals[i];
+    labels[i]       = identity ? static_cast<VT>(v) : sorted_vertices[v];
+    new_of_sorted[v] = static_cast<uint32_t>(i);
+    sorted_deg[i]   = maxdeg - sorted_keys[i];
+  }
+}
+
+// number of leading elements of the descending array `deg` that are >= t
+// (thrust::upper_bound(..., greater) of renumber_edgelist_impl.cuh:436-442)
+__global__ void segment_bounds_kernel(const uint32_t* deg, int64_t n, const int64_t* thresholds,
+                                      int nt, int64_t* out)
+{
+  int k = threadIdx.x;
+  if (k >= nt) return;
+  int64_t t  = thresholds[k];
+  int64_t lo = 0, hi = n;
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if (static_cast<int64_t>(deg[mid]) >= t) lo = mid + 1;
+    else hi = mid;
+  }
+  out[k] = lo;
+}
+
+template <typename VT>
+__global__ void edge_keys_kernel(const VT* majors, const VT* minors, size_t n,
+                                 vertex_lookup<VT> lk, const uint32_t* new_of_sorted,
+                                 uint64_t* keys, uint32_t* vals, int* bad)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    int64_t pj = lk(majors[i]);
+    int64_t pn = lk(minors[i]);
+    if (pn < 0 || pn >= lk.n || (lk.mode == 2 && lk.sorted[pn] != minors[i])) {
+      *bad = 1;
+      pn   = 0;
+    }
+    uint32_t mj = new_of_sorted ? new_of_sorted[pj] : static_cast<uint32_t>(pj);
+    uint32_t mn = new_of_sorted ? new_of_sorted[pn] : static_cast<uint32_t>(pn);
+    keys[i]     = (static_cast<uint64_t>(mj) << 32) | mn;
+    vals[i]     = static_cast<uint32_t>(i);
+  }
+}
+
+template <typename WT>
+__global__ void finish_edges_kernel(const uint64_t* keys, const uint32_t* vals, size_t n,
+                                    const WT* w_in, int32_t* indices, WT* w_out)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    indices[i] = static_cast<int32_t>(keys[i] & 0xffffffffu);
+    if (w_in) w_out[i] = w_in[vals[i]];
+  }
+}
+
+template <typename ET>
+__global__ void narrow_offsets_kernel(const uint64_t* in, size_t n, ET* out)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    out[i] = static_cast<ET>(in[i]);
+}
+
+template <typename VT>
+__global__ void iota_kernel(VT* out, size_t n, VT first)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    out[i] = first + static_cast<VT>(i);
+}
+
+template <typename WT>
+__global__ void out_weight_kernel(const int32_t* indices, const WT* w, size_t n, double* out)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    atomicAdd(&out[indices[i]], static_cast<double>(w[i]));
+}
+__global__ void out_degree_kernel(const int32_t* indices, size_t n, unsigned long long* out)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    atomicAdd(&out[indices[i]], 1ull);
+}
+__global__ void u64_to_double_kernel(const unsigned long long* in, size_t n, double* out)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    out[i] = static_cast<double>(in[i]);
+}
+
+template <typename ET>
+__global__ void in_degree_kernel(const ET* offsets, size_t n, ET* out)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    out[i] = offsets[i + 1] - offsets[i];
+}
+
+// ---- tile schedule ---------------------------------------------------------------------
+// kind-0 tiles: window k of T edges over the edge range of rows [row_lo, row_hi) owns the
+// rows whose FIRST edge lies in the window.
+template <typename ET>
+__global__ void row_tiles_kernel(const ET* offsets, int64_t row_lo, int64_t row_hi,
+                                 int64_t edge_lo, int T, int64_t ntiles, tile_t* tiles)
+{
+  int64_t k = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  if (k >= ntiles) return;
+  auto lower = [&](int64_t target) {
+    int64_t lo = row_lo, hi = row_hi;
+    while (lo < hi) {
+      int64_t mid = (lo + hi) >> 1;
+      if (static_cast<int64_t>(offsets[mid]) < target) lo = mid + 1;
+      else hi = mid;
+    }
+    return lo;
+  };
+  int64_t r0 = lower(edge_lo + k * T);
+  int64_t r1 = (k + 1 == ntiles) ? row_hi : lower(edge_lo + (k + 1) * T);
+  tile_t t;
+  t.edge_first = static_cast<int64_t>(offsets[r0]);
+  t.num_edges  = static_cast<int32_t>(static_cast<int64_t>(offsets[r1]) - t.edge_first);
+  t.row_first  = static_cast<int32_t>(r0);
+  t.num_rows   = static_cast<int32_t>(r1 - r0);
+  t.aux        = 0;
+  t.kind       = 0;
+  t.pad        = 0;
+  tiles[k]     = t;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------
+// schedule
+// ------------------------------------------------------------------------------------------
+template <typename ET>
+static void build_schedule_t(b200_handle* h, edge_partition& ep, int T)
+{
+  cudaStream_t s = h->stream;
+  const ET* off  = reinterpret_cast<const ET*>(ep.offsets.data());
+  // rows [0, n_long) are split into chunks; rows [n_long, n_nz) are packed into row tiles
+  int64_t n_long = ep.has_segments ? ep.seg[1] : 0;
+  int64_t n_nz   = ep.has_segments ? ep.seg[3] : ep.num_rows;
+  std::vector<ET> h_off(static_cast<size_t>(n_long) + 1);
+  CUDA_TRY(cudaMemcpyAsync(h_off.data(), off, h_off.size() * sizeof(ET), cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaStreamSynchronize(s));
+  std::vector<tile_t> chunk_tiles;
+  std::vector<int64_t> chunk_first(static_cast<size_t>(n_long) + 1, 0);
+  for (int64_t r = 0; r < n_long; ++r) {
+    int64_t b = h_off[r], e = h_off[r + 1];
+    chunk_first[r] = static_cast<int64_t>(chunk_tiles.size());
+    for (int64_t c = b; c < e; c += T) {
+      tile_t t{};
+      t.edge_first = c;
+      t.num_edges  = static_cast<int32_t>(std::min<int64_t>(T, e - c));
+      t.row_first  = static_cast<int32_t>(r);
+      t.num_rows   = 1;
+      t.aux        = static_cast<int32_t>(chunk_tiles.size());
+      t.kind       = 1;
+      chunk_tiles.push_back(t);
+    }
+  }
+  chunk_first[n_long] = static_cast<int64_t>(chunk_tiles.size());
+  int64_t edge_lo     = h_off[n_long];
+  int64_t n_row_tiles = (n_nz > n_long) ? div_up(ep.num_edges - edge_lo, T) : 0;
+  if (n_nz > n_long && n_row_tiles == 0) n_row_tiles = 1;  // rows present but no edges
+  ep.num_chunks    = static_cast<int64_t>(chunk_tiles.size());
+  ep.num_long_rows = n_long;
+  ep.num_tiles     = ep.num_chunks + n_row_tiles;
+  ep.tiles.alloc(static_cast<size_t>(ep.num_tiles), s);
+  if (!chunk_tiles.empty())
+    CUDA_TRY(cudaMemcpyAsync(ep.tiles.data(), chunk_tiles.data(), chunk_tiles.size() * sizeof(tile_t),
+                             cudaMemcpyHostToDevice, s));
+  ep.long_row_chunk_first.alloc(chunk_first.size(), s);
+  CUDA_TRY(cudaMemcpyAsync(ep.long_row_chunk_first.data(), chunk_first.data(),
+                           chunk_first.size() * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+  if (n_row_tiles > 0) {
+    row_tiles_kernel<ET><<<grid_for(n_row_tiles), kThreads, 0, s>>>(
+      off, n_long, n_nz, edge_lo, T, n_row_tiles, ep.tiles.data() + ep.num_chunks);
+    CUDA_TRY(cudaGetLastError());
+  }
+  CUDA_TRY(cudaStreamSynchronize(s));
+  ep.sched_tile_edges = T;
+}
+
+void build_schedule(b200_handle* h, edge_partition& ep, int T)
+{
+  if (ep.sched_tile_edges == T) return;
+  if (ep.offsets64) build_schedule_t<int64_t>(h, ep, T);
+  else build_schedule_t<int32_t>(h, ep, T);
+}
+
+// ------------------------------------------------------------------------------------------
+// single-GPU build
+// ------------------------------------------------------------------------------------------
+template <typename VT>
+static void build_partition_from_coo(b200_handle* h, const VT* majors, const VT* minors,
+                                     const void* weights, int weight_type, size_t ne,
+                                     vertex_lookup<VT> lk, const uint32_t* new_of_sorted,
+                                     const uint32_t* sorted_deg, int64_t nv, edge_partition& ep)
+{
+  // keys -> stable sort -> indices / weights; offsets = scan(sorted degrees)
+  cudaStream_t s = h->stream;
+  ep.num_rows    = nv;
+  ep.num_edges   = static_cast<int64_t>(ne);
+  ep.num_minors  = nv;
+  ep.offsets64   = ne >= static_cast<size_t>(0x7fffffff);  // c_api/graph_sg.cpp: int32_threshold
+  int vbits      = bits_needed(nv > 0 ? static_cast<uint64_t>(nv - 1) : 0);
+
+  dbuf<uint64_t> k0(ne, s), k1(ne, s);
+  dbuf<uint32_t> v0(ne, s), v1(ne, s);
+  dbuf<int> bad(1, s);
+  CUDA_TRY(cudaMemsetAsync(bad.data(), 0, sizeof(int), s));
+  if (ne) {
+    edge_keys_kernel<VT><<<grid_for(ne, 4), kThreads, 0, s>>>(majors, minors, ne, lk, new_of_sorted,
+                                                            k0.data(), v0.data(), bad.data());
+    CUDA_TRY(cudaGetLastError());
+  }
+  int h_bad = 0;
+  CUDA_TRY(cudaMemcpyAsync(&h_bad, bad.data(), sizeof(int), cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaStreamSynchronize(s));
+  B200_EXPECTS(!h_bad, kInvalidInput,
+               "Invalid input argument: edge endpoints are not in the vertex list.");
+  int where = radix_sort<uint64_t>(k0.data(), k1.data(), v0.data(), v1.data(), ne,
+                                   {{0, vbits}, {32, 32 + vbits}}, s);
+  uint64_t* ks = where ? k1.data() : k0.data();
+  uint32_t* vs = where ? v1.data() : v0.data();
+
+  ep.indices.alloc(ne, s, 16);
+  if (weights) {
+    ep.weights.alloc(ne * dtype_size(weight_type), s, 32);
+    if (ne) {
+      if (weight_type == B200_FLOAT32)
+        finish_edges_kernel<float><<<grid_for(ne, 4), kThreads, 0, s>>>(
+          ks, vs, ne, static_cast<const float*>(weights), ep.indices.data(),
+          reinterpret_cast<float*>(ep.weights.data()));
+      else
+        finish_edges_kernel<double><<<grid_for(ne, 4), kThreads, 0, s>>>(
+          ks, vs, ne, static_cast<const double*>(weights), ep.indices.data(),
+          reinterpret_cast<double*>(ep.weights.data()));
+      CUDA_TRY(cudaGetLastError());
+    }
+  } else if (ne) {
+    finish_edges_kernel<float><<<grid_for(ne, 4), kThreads, 0, s>>>(ks, vs, ne, nullptr,
+                                                                   ep.indices.data(), nullptr);
+    CUDA_TRY(cudaGetLastError());
+  }
+  // offsets
+  dbuf<uint64_t> off64(static_cast<size_t>(nv) + 1, s);
+  exclusive_scan<uint32_t, uint64_t>(sorted_deg, off64.data(), static_cast<size_t>(nv), s, true);
+  if (ep.offsets64) {
+    ep.offsets.alloc((static_cast<size_t>(nv) + 1) * 8, s, 64);
+    CUDA_TRY(cudaMemcpyAsync(ep.offsets.data(), off64.data(), (static_cast<size_t>(nv) + 1) * 8,
+                             cudaMemcpyDeviceToDevice, s));
+  } else {
+    ep.offsets.alloc((static_cast<size_t>(nv) + 1) * 4, s, 64);
+    narrow_offsets_kernel<int32_t><<<grid_for(nv + 1, 4), kThreads, 0, s>>>(
+      off64.data(), static_cast<size_t>(nv) + 1, reinterpret_cast<int32_t*>(ep.offsets.data()));
+    CUDA_TRY(cudaGetLastError());
+  }
+  CUDA_TRY(cudaStreamSynchronize(s));
+}
+
+template <typename VT>
+static void create_sg_t(b200_handle* h, const VT* src, const VT* dst, const void* weights,
+                        size_t ne, int weight_type, const VT* vertices, size_t n_given,
+                        bool store_transposed, bool renumber, b200_graph* g)
+{
+  cudaStream_t s   = h->stream;
+  const VT* majors = store_transposed ? dst : src;
+  const VT* minors = store_transposed ? src : dst;
+
+  // ---- 1. sorted unique vertex list (renumber_edgelist_impl.cuh:96-217) ----
+  dbuf<unsigned long long> d_max(1, s);
+  dbuf<int> d_flag(1, s);
+  CUDA_TRY(cudaMemsetAsync(d_max.data(), 0, 8, s));
+  CUDA_TRY(cudaMemsetAsync(d_flag.data(), 0, 4, s));
+  if (ne) {
+    max_id_kernel<VT><<<std::min(grid_for(ne, 8), 4096u), kThreads, 0, s>>>(src, dst, ne, d_max.data(),
+                                                                        d_flag.data());
+    CUDA_TRY(cudaGetLastError());
+  }
+  if (vertices && n_given) {
+    max_id_kernel<VT><<<std::min(grid_for(n_given, 8), 4096u), kThreads, 0, s>>>(
+      vertices, nullptr, n_given, d_max.data(), d_flag.data());
+    CUDA_TRY(cudaGetLastError());
+  }
+  unsigned long long h_max = 0;
+  int h_flag               = 0;
+  CUDA_TRY(cudaMemcpyAsync(&h_max, d_max.data(), 8, cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaMemcpyAsync(&h_flag, d_flag.data(), 4, cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaStreamSynchronize(s));
+  B200_EXPECTS(!h_flag, kInvalidInput, "Invalid input argument: vertex ids should be non-negative.");
+  bool empty = (ne == 0) && !(vertices && n_given);
+
+  int64_t nv = 0;
+  dbuf<VT> sorted_vertices;
+  dbuf<uint32_t> pos;  // direct map id -> position (mode 1)
+  vertex_lookup<VT> lk{0, nullptr, nullptr, 0};
+  if (empty) {
+    nv = 0;
+  } else if (!renumber) {
+    // ids are the internal ids; V = max id + 1 (or the given list, which must be 0..V-1)
+    nv = static_cast<int64_t>(h_max) + 1;
+    if (vertices && n_given) nv = std::max<int64_t>(nv, static_cast<int64_t>(n_given));
+    lk = {0, nullptr, nullptr, nv};
+  } else {
+    size_t span = static_cast<size_t>(h_max) + 1;
+    bool identity = false;
+    if (vertices && n_given == span) {
+      CUDA_TRY(cudaMemsetAsync(d_flag.data(), 0, 4, s));
+      is_identity_kernel<VT><<<std::min(grid_for(n_given, 8), 4096u), kThreads, 0, s>>>(vertices, n_given,
+                                                                                    d_flag.data());
+      CUDA_TRY(cudaGetLastError());
+      CUDA_TRY(cudaMemcpyAsync(&h_flag, d_flag.data(), 4, cudaMemcpyDeviceToHost, s));
+      CUDA_TRY(cudaStreamSynchronize(s));
+      identity = !h_flag;
+    }
+    if (identity) {
+      nv = static_cast<int64_t>(span);
+      lk = {0, nullptr, nullptr, nv};
+    } else if (span <= std::max<size_t>(size_t{1} << 26, 8 * (ne + n_given))) {
+      // dense-ish id space: presence flags + scan (same result as sort + unique)
+      dbuf<uint32_t> flags(span, s);
+      CUDA_TRY(cudaMemsetAsync(flags.data(), 0, span * 4, s));
+      if (vertices && n_given) {
+        mark_present_kernel<VT><<<grid_for(n_given, 4), kThreads, 0, s>>>(vertices, nullptr, n_given,
+                                                                        flags.data());
+      } else {
+        mark_present_kernel<VT><<<grid_for(ne, 4), kThreads, 0, s>>>(src, dst, ne, flags.data());
+      }
+      CUDA_TRY(cudaGetLastError());
+      pos.alloc(span + 1, s);
+      exclusive_scan<uint32_t, uint32_t>(flags.data(), pos.data(), span, s, true);
+      uint32_t h_nv = 0;
+      CUDA_TRY(cudaMemcpyAsync(&h_nv, pos.data() + span, 4, cudaMemcpyDeviceToHost, s));
+      CUDA_TRY(cudaStreamSynchronize(s));
+      nv = h_nv;
+      sorted_vertices.alloc(static_cast<size_t>(nv), s);
+      compact_present_kernel<VT><<<grid_for(span, 4), kThreads, 0, s>>>(flags.data(), pos.data(), span,
+                                                                      sorted_vertices.data());
+      CUDA_TRY(cudaGetLastError());
+      CUDA_TRY(cudaStreamSynchronize(s));
+      lk = {1, pos.data(), sorted_vertices.data(), nv};
+    } else {
+      // sparse id space: radix sort + unique, lookups by binary search
+      size_t n_all = (vertices && n_given) ? n_given : 2 * ne;
+      dbuf<uint64_t> a(n_all, s), b(n_all, s);
+      {
+        dbuf<VT> tmp;  // widen to u64 keys
+        extern void launch_widen_ids(const void*, const void*, size_t, int, uint64_t*, cudaStream_t);
+        if (vertices && n_given) launch_widen_ids(vertices, nullptr, n_given, sizeof(VT), a.data(), s);
+        else launch_widen_ids(src, dst, ne, sizeof(VT), a.data(), s);
+      }
+      int where = radix_sort<uint64_t>(a.data(), b.data(), nullptr, nullptr, n_all,
+                                       {{0, bits_needed(h_max)}}, s);
+      uint64_t* srt = where ? b.data() : a.data();
+      extern int64_t launch_unique_ids(const uint64_t*, size_t, int, void*, cudaStream_t);
+      sorted_vertices.alloc(n_all, s);
+      nv = launch_unique_ids(srt, n_all, sizeof(VT), sorted_vertices.data(), s);
+      lk = {2, nullptr, sorted_vertices.data(), nv};
+    }
+  }
+  B200_EXPECTS(nv < (int64_t{1} << 31), kInvalidInput,
+               "number of vertices must fit 32-bit internal ids");
+
+  g->num_vertices = nv;
+  g->num_edges    = static_cast<int64_t>(ne);
+  g->local_first  = 0;
+  g->local_last   = nv;
+  g->renumbered   = renumber;
+  g->parts.resize(1);
+  edge_partition& ep = g->parts[0];
+
+  // ---- 2. major degrees (renumber_edgelist_impl.cuh:219-382) ----
+  dbuf<uint32_t> deg(static_cast<size_t>(nv), s);
+  CUDA_TRY(cudaMemsetAsync(deg.data(), 0, static_cast<size_t>(nv) * 4 + (nv == 0 ? 4 : 0), s));
+  CUDA_TRY(cudaMemsetAsync(d_flag.data(), 0, 4, s));
+  if (ne) {
+    count_degree_kernel<VT><<<grid_for(ne, 4), kThreads, 0, s>>>(majors, ne, lk, deg.data(),
+                                                               d_flag.data());
+    CUDA_TRY(cudaGetLastError());
+  }
+  CUDA_TRY(cudaMemcpyAsync(&h_flag, d_flag.data(), 4, cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaStreamSynchronize(s));
+  B200_EXPECTS(!h_flag, kInvalidInput,
+               "Invalid input argument: edge endpoints are not in the vertex list.");
+
+  dbuf<uint32_t> new_of_sorted;
+  dbuf<uint32_t> sorted_deg(static_cast<size_t>(nv), s);
+  g->renumber_map.alloc(static_cast<size_t>(nv) * sizeof(VT), s);
+  VT* labels = reinterpret_cast<VT*>(g->renumber_map.data());
+
+  if (renumber && nv > 0) {
+    // ---- 3. stable sort by descending degree (renumber_edgelist_impl.cuh:384-390) ----
+    dbuf<uint32_t> d_maxdeg(1, s);
+    CUDA_TRY(cudaMemsetAsync(d_maxdeg.data(), 0, 4, s));
+    max_u32_kernel<<<std::min(grid_for(nv, 8), 4096u), kThreads, 0, s>>>(deg.data(), nv, d_maxdeg.data());
+    CUDA_TRY(cudaGetLastError());
+    uint32_t maxdeg = 0;
+    CUDA_TRY(cudaMemcpyAsync(&maxdeg, d_maxdeg.data(), 4, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    dbuf<uint32_t> k0(nv, s), k1(nv, s), v0(nv, s), v1(nv, s);
+    degree_keys_kernel<<<grid_for(nv, 4), kThreads, 0, s>>>(deg.data(), nv, maxdeg, k0.data(), v0.data());
+    CUDA_TRY(cudaGetLastError());
+    int where = radix_sort<uint32_t>(k0.data(), k1.data(), v0.data(), v1.data(), nv,
+                                     {{0, bits_needed(maxdeg)}}, s);
+    new_of_sorted.alloc(nv, s);
+    finish_renumber_kernel<VT><<<grid_for(nv, 4), kThreads, 0, s>>>(
+      where ? k1.data() : k0.data(), where ? v1.data() : v0.data(), nv, maxdeg,
+      sorted_vertices.data(), lk.mode == 0, labels, new_of_sorted.data(), sorted_deg.data());
+    CUDA_TRY(cudaGetLastError());
+
+    // ---- 4. segment offsets (renumber_edgelist_impl.cuh:392-449) ----
+    std::vector<int64_t> thr{kMidDegreeThreshold, kLowDegreeThreshold, 1};
+    dbuf<int64_t> d_thr(thr.size(), s), d_seg(thr.size(), s);
+    CUDA_TRY(cudaMemcpyAsync(d_thr.data(), thr.data(), thr.size() * 8, cudaMemcpyHostToDevice, s));
+    segment_bounds_kernel<<<1, 32, 0, s>>>(sorted_deg.data(), nv, d_thr.data(),
+                                           static_cast<int>(thr.size()), d_seg.data());
+    CUDA_TRY(cudaGetLastError());
+    std::vector<int64_t> h_seg(thr.size());
+    CUDA_TRY(cudaMemcpyAsync(h_seg.data(), d_seg.data(), thr.size() * 8, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    g->num_segments       = 4;
+    g->segment_offsets[0] = 0;
+    for (int i = 0; i < 3; ++i) g->segment_offsets[i + 1] = h_seg[i];
+    g->segment_offsets[4] = nv;
+    ep.has_segments       = true;
+    for (int i = 0; i < 5; ++i) ep.seg[i] = g->segment_offsets[i];
+  } else {
+    if (nv > 0) {
+      iota_kernel<VT><<<grid_for(nv, 4), kThreads, 0, s>>>(labels, nv, VT(0));
+      CUDA_TRY(cudaGetLastError());
+      CUDA_TRY(cudaMemcpyAsync(sorted_deg.data(), deg.data(), static_cast<size_t>(nv) * 4,
+                               cudaMemcpyDeviceToDevice, s));
+    }
+    g->num_segments = 0;
+    ep.has_segments = false;
+  }
+
+  // ---- 5. renumber edges + compress + neighbour sort ----
+  build_partition_from_coo<VT>(h, majors, minors, weights, weight_type, ne, lk,
+                               (renumber && nv > 0) ? new_of_sorted.data() : nullptr,
+                               sorted_deg.data(), nv, ep);
+  ep.major_first = 0;
+  ep.minor_first = 0;
+  if (!ep.has_segments) { ep.seg[0] = 0; ep.seg[1] = 0; ep.seg[2] = 0; ep.seg[3] = nv; ep.seg[4] = nv; }
+  g->edge_type = ep.offsets64 ? B200_INT64 : B200_INT32;
+}
+
+void graph_out_weight_sums(b200_handle* h, b200_graph* g)
+{
+  if (g->have_out_weight_sums) return;
+  cudaStream_t s = h->stream;
+  B200_EXPECTS(!g->multi_gpu, kNotImplemented, "out-weight sums of MG graphs are built by mg.cu");
+  edge_partition& ep = g->parts[0];
+  size_t nv          = static_cast<size_t>(g->num_vertices);
+  size_t ne          = static_cast<size_t>(ep.num_edges);
+  g->out_weight_sums.alloc(nv, s);
+  if (g->weighted) {
+    CUDA_TRY(cudaMemsetAsync(g->out_weight_sums.data(), 0, std::max<size_t>(nv, 1) * 8, s));
+    if (ne) {
+      if (g->weight_type == B200_FLOAT32)
+        out_weight_kernel<float><<<grid_for(ne, 4), kThreads, 0, s>>>(
+          ep.indices.data(), reinterpret_cast<const float*>(ep.weights.data()), ne,
+          g->out_weight_sums.data());
+      else
+        out_weight_kernel<double><<<grid_for(ne, 4), kThreads, 0, s>>>(
+          ep.indices.data(), reinterpret_cast<const double*>(ep.weights.data()), ne,
+          g->out_weight_sums.data());
+      CUDA_TRY(cudaGetLastError());
+    }
+  } else {
+    dbuf<unsigned long long> cnt(nv, s);
+    CUDA_TRY(cudaMemsetAsync(cnt.data(), 0, std::max<size_t>(nv, 1) * 8, s));
+    if (ne) {
+      out_degree_kernel<<<grid_for(ne, 4), kThreads, 0, s>>>(ep.indices.data(), ne, cnt.data());
+      CUDA_TRY(cudaGetLastError());
+    }
+    if (nv) {
+      u64_to_double_kernel<<<grid_for(nv, 4), kThreads, 0, s>>>(cnt.data(), nv,
+                                                                g->out_weight_sums.data());
+      CUDA_TRY(cudaGetLastError());
+    }
+    CUDA_TRY(cudaStreamSynchronize(s));
+  }
+  CUDA_TRY(cudaStreamSynchronize(s));
+  g->have_out_weight_sums = true;
+}
+
+// small helpers referenced above (kept out of templates to have one definition)
+__global__ void widen_ids_kernel32(const int32_t* a, const int32_t* b, size_t n, uint64_t* out)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    out[i] = static_cast<uint64_t>(a[i]);
+    if (b) out[n + i] = static_cast<uint64_t>(b[i]);
+  }
+}
+__global__ void widen_ids_kernel64(const int64_t* a, const int64_t* b, size_t n, uint64_t* out)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    out[i] = static_cast<uint64_t>(a[i]);
+    if (b) out[n + i] = static_cast<uint64_t>(b[i]);
+  }
+}
+void launch_widen_ids(const void* a, const void* b, size_t n, int width, uint64_t* out,
+                      cudaStream_t s)
+{
+  if (n == 0) return;
+  if (width == 4)
+    widen_ids_kernel32<<<grid_for(n, 4), kThreads, 0, s>>>(static_cast<const int32_t*>(a),
+                                                          static_cast<const int32_t*>(b), n, out);
+  else
+    widen_ids_kernel64<<<grid_for(n, 4), kThreads, 0, s>>>(static_cast<const int64_t*>(a),
+                                                          static_cast<const int64_t*>(b), n, out);
+  CUDA_TRY(cudaGetLastError());
+}
+__global__ void unique_flags_kernel(const uint64_t* sorted, size_t n, uint32_t* flags)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    flags[i] = (i == 0 || sorted[i] != sorted[i - 1]) ? 1u : 0u;
+}
+template <typename VT>
+__global__ void unique_compact_kernel(const uint64_t* sorted, const uint32_t* flags,
+                                      const uint32_t* pos, size_t n, VT* out)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    if (flags[i]) out[pos[i]] = static_cast<VT>(sorted[i]);
+}
+int64_t launch_unique_ids(const uint64_t* sorted, size_t n, int width, void* out, cudaStream_t s)
+{
+  if (n == 0) return 0;
+  dbuf<uint32_t> flags(n, s), pos(n + 1, s);
+  unique_flags_kernel<<<grid_for(n, 4), kThreads, 0, s>>>(sorted, n, flags.data());
+  CUDA_TRY(cudaGetLastError());
+  exclusive_scan<uint32_t, uint32_t>(flags.data(), pos.data(), n, s, true);
+  uint32_t cnt = 0;
+  CUDA_TRY(cudaMemcpyAsync(&cnt, pos.data() + n, 4, cudaMemcpyDeviceToHost, s));
+  if (width == 4)
+    unique_compact_kernel<int32_t><<<grid_for(n, 4), kThreads, 0, s>>>(sorted, flags.data(), pos.data(),
+                                                                     n, static_cast<int32_t*>(out));
+  else
+    unique_compact_kernel<int64_t><<<grid_for(n, 4), kThreads, 0, s>>>(sorted, flags.data(), pos.data(),
+                                                                     n, static_cast<int64_t*>(out));
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaStreamSynchronize(s));
+  return cnt;
+}
+
+void graph_create_sg(b200_handle* h, const void* src, const void* dst, const void* weights,
+                     size_t ne, int vertex_type, int weight_type, const void* vertices,
+                     size_t n_given, bool store_transposed, bool renumber, b200_graph* g)
+{
+  g->vertex_type      = vertex_type;
+  g->weight_type      = weights ? weight_type : B200_FLOAT32;
+  g->weighted         = weights != nullptr;
+  g->store_transposed = store_transposed;
+  g->multi_gpu        = false;
+  if (vertex_type == B200_INT32)
+    create_sg_t<int32_t>(h, static_cast<const int32_t*>(src), static_cast<const int32_t*>(dst),
+                         weights, ne, weight_type, static_cast<const int32_t*>(vertices), n_given,
+                         store_transposed, renumber, g);
+  else
+    create_sg_t<int64_t>(h, static_cast<const int64_t*>(src), static_cast<const int64_t*>(dst),
+                         weights, ne, weight_type, static_cast<const int64_t*>(vertices), n_given,
+                         store_transposed, renumber, g);
+}
+
+void graph_in_degrees(b200_handle* h, const b200_graph* g, void* out)
+{
+  const edge_partition& ep = g->parts[0];
+  size_t nv                = static_cast<size_t>(ep.num_rows);
+  if (nv == 0) return;
+  if (ep.offsets64)
+    in_degree_kernel<int64_t><<<grid_for(nv, 4), kThreads, 0, h->stream>>>(
+      reinterpret_cast<const int64_t*>(ep.offsets.data()), nv, static_cast<int64_t*>(out));
+  else
+    in_degree_kernel<int32_t><<<grid_for(nv, 4), kThreads, 0, h->stream>>>(
+      reinterpret_cast<const int32_t*>(ep.offsets.data()), nv, static_cast<int32_t*>(out));
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+}
+
+}  // namespace b200

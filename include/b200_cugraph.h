@@ -1,0 +1,205 @@
+/*
+ * b200_cugraph.h — raw-pointer C ABI of the B200-native pull-SpMV / PageRank engine.
+ *
+ * This is the boundary a libcugraph maintainer binds: plain pointers and sizes, no C++ or
+ * torch types.  Every entry point names the reference interface it stands in for (paths are
+ * relative to the reference tree).  The cugraph_c-compatible layer (include/cugraph_c/*.h,
+ * cugraph_forked_b200/csrc/c_api.cu) and the Python mirror of pylibcugraph both sit on top
+ * of exactly these calls.
+ *
+ * Conventions
+ *   - all array arguments are DEVICE pointers unless the name starts with h_;
+ *   - every function returns 0 on success or a cugraph_error_code_t value
+ *     (cpp/include/cugraph_c/error.h:25-33); b200_last_error() returns the message of the
+ *     last failure on the calling thread (the reference throws cugraph::logic_error with the
+ *     same texts, cpp/include/cugraph/utilities/error.hpp:33-49);
+ *   - dtype ids are the reference's data_type_id_t (cpp/include/cugraph_c/resource_handle.h):
+ *     INT32=0, INT64=1, FLOAT32=2, FLOAT64=3;
+ *   - calls are synchronous from the caller's view (they return after the work on the
+ *     handle's stream has completed), as the reference's are.
+ */
+#ifndef B200_CUGRAPH_H
+#define B200_CUGRAPH_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_INT32 0
+#define B200_INT64 1
+#define B200_FLOAT32 2
+#define B200_FLOAT64 3
+
+/* -------------------------------------------------------------------------------------------
+ * handle  — stands in for raft::handle_t (stream + comms), cpp/src/c_api/resource_handle.cpp:21-43
+ * ------------------------------------------------------------------------------------------- */
+typedef struct b200_handle b200_handle_t;
+
+/* stream = cudaStream_t (NULL: a private non-blocking stream is created). */
+int b200_handle_create(void* stream, b200_handle_t** out);
+/* Multi-GPU handle: one process per GPU.  nccl_unique_id = the 128-byte ncclUniqueId produced
+ * by b200_nccl_unique_id() on rank 0 and distributed by the launcher (torch.distributed / MPI).
+ * row_comm_size = R of the reference's R x C grid (partition_manager.hpp:70-113); the row and
+ * column sub-communicators are split exactly as the reference does: row_comm colour =
+ * rank / R, col_comm colour = rank % R. */
+int b200_handle_create_mg(void* stream, const void* nccl_unique_id, int rank, int world_size,
+                          int row_comm_size, b200_handle_t** out);
+int b200_nccl_unique_id(void* out_128_bytes);
+int b200_handle_rank(const b200_handle_t* h);       /* cugraph_resource_handle_get_rank */
+int b200_handle_world_size(const b200_handle_t* h);
+void b200_handle_free(b200_handle_t* h);
+const char* b200_last_error(void);
+
+/* -------------------------------------------------------------------------------------------
+ * graph — stands in for graph_t<vertex_t,edge_t,weight_t,store_transposed,false> +
+ * create_graph_from_edgelist (cpp/src/structure/create_graph_from_edgelist_impl.cuh:570-774):
+ * renumber by descending major degree (renumber_edgelist_impl.cuh:96-452), COO -> CSC/CSR with
+ * ascending neighbours (structure/detail/structure_utils.cuh:173-490), degree segments
+ * (graph_view.hpp:255-263).
+ * ------------------------------------------------------------------------------------------- */
+typedef struct b200_graph b200_graph_t;
+
+typedef struct b200_graph_view {
+  /* POD mirror of edge_partition_device_view_t (edge_partition_device_view.cuh:355-483) plus
+   * the host metadata of graph_view_t (graph_view.hpp:838+). Device pointers stay owned by
+   * the graph. */
+  int64_t num_vertices;
+  int64_t num_edges;
+  int32_t vertex_type;      /* B200_INT32 | B200_INT64 (ids as given by the caller)            */
+  int32_t edge_type;        /* type of offsets: INT32 unless num_edges >= 2^31-1                */
+  int32_t weight_type;      /* B200_FLOAT32 | B200_FLOAT64; meaningful when weights != NULL     */
+  int32_t store_transposed; /* 1: rows are destinations (CSC, the pull layout)                  */
+  int32_t renumbered;
+  int32_t num_segments;     /* entries in segment_offsets minus 1 (4 for single GPU), 0 if none */
+  int64_t segment_offsets[8]; /* [0, n_high, n_high+n_mid, n_nonzero, V] when renumbered        */
+  const void* offsets;      /* edge_type  [num_vertices + 1]                                    */
+  const void* indices;      /* int32      [num_edges]  (internal ids are always 32-bit)         */
+  const void* weights;      /* weight_type[num_edges] or NULL                                   */
+  const void* renumber_map; /* vertex_type[num_vertices]: internal id -> external id            */
+  /* multi-GPU only (zero / NULL on a single GPU) */
+  int32_t comm_rank, comm_size, row_comm_size, col_comm_size;
+  int64_t local_vertex_first, local_vertex_last; /* this rank's vertex partition (internal ids) */
+} b200_graph_view_t;
+
+/* Single-GPU graph from a COO edge list (external ids).  vertices may be NULL (vertex set =
+ * ids that appear in an edge, as cugraph_sg_graph_create does, c_api/graph_sg.cpp:61-190) or
+ * list every vertex including isolated ones (as the C++ tests' Rmat_Usecase does,
+ * cpp/tests/utilities/test_graphs.hpp:329-347).  renumber = 0 requires ids in [0, V). */
+int b200_graph_create_sg(b200_handle_t* h, const void* src, const void* dst, const void* weights,
+                         size_t num_edges, int vertex_type, int weight_type, const void* vertices,
+                         size_t num_vertices, int store_transposed, int renumber,
+                         b200_graph_t** out);
+/* Multi-GPU graph: each rank passes the edges it currently holds (any distribution); they are
+ * shuffled to their 2D owner (shuffle_wrappers.cu:41-174), vertices hash-assigned to ranks
+ * (graph_utils.cuh:45-53), renumbered and compressed per local edge partition
+ * (create_graph_from_edgelist_impl.cuh:207-555). */
+int b200_graph_create_mg(b200_handle_t* h, const void* src, const void* dst, const void* weights,
+                         size_t num_local_edges, int vertex_type, int weight_type,
+                         const void* local_vertices, size_t num_local_vertices,
+                         int store_transposed, b200_graph_t** out);
+int b200_graph_view(const b200_graph_t* g, b200_graph_view_t* out);
+/* view of local edge partition i (0 <= i < col_comm_size) of a multi-GPU graph */
+int b200_graph_partition_view(const b200_graph_t* g, int i, b200_graph_view_t* out);
+void b200_graph_free(b200_graph_t* g);
+
+/* graph_view_t::compute_out_weight_sums (cpp/src/structure/graph_view_impl.cuh:238-265,
+ * :696-721): per-source sum of edge weights (out-degree when unweighted), internal order.
+ * out: value_type[local vertices]. Cached inside the graph after the first call. */
+int b200_graph_out_weight_sums(b200_handle_t* h, b200_graph_t* g, int value_type, void* out);
+/* in-degrees = per-row edge counts (graph_view_t::compute_in_degrees, graph_view_impl.cuh:203-219);
+ * out: edge_type[local vertices] */
+int b200_graph_in_degrees(b200_handle_t* h, const b200_graph_t* g, void* out);
+
+/* -------------------------------------------------------------------------------------------
+ * the hot path — per_v_transform_reduce_incoming_e
+ * (cpp/src/prims/per_v_transform_reduce_incoming_outgoing_e.cuh:1082, :489-1038) specialised
+ * to the edge ops of its three callers:  y[dst] = init + scale * sum_{src->dst} x[src] * w
+ * x, y: value_type[num_vertices] in internal order (single GPU).
+ * ------------------------------------------------------------------------------------------- */
+int b200_spmv_pull(b200_handle_t* h, const b200_graph_t* g, int value_type, const void* x,
+                   double scale, double init, void* y);
+
+/* -------------------------------------------------------------------------------------------
+ * drivers
+ * ------------------------------------------------------------------------------------------- */
+typedef struct b200_centrality_stats {
+  int64_t iterations;   /* power iterations executed                                           */
+  int32_t converged;    /* 1 when the stop test passed                                         */
+  double last_diff;     /* L1 difference of the last executed iteration                        */
+  double elapsed_ms;    /* device time of the iteration loop (CUDA events on the handle stream) */
+  int64_t gpu_launches; /* kernels launched by the loop                                        */
+} b200_centrality_stats_t;
+
+typedef struct b200_pagerank_params {
+  double alpha;
+  double epsilon;
+  uint64_t max_iterations;
+  int32_t value_type;                  /* result_t: B200_FLOAT32 | B200_FLOAT64                 */
+  int32_t has_initial_guess;           /* pageranks[] holds the guess on entry                  */
+  const void* precomputed_out_weight_sums; /* value_type[local V], internal order, or NULL      */
+  const void* personalization_vertices;    /* INTERNAL ids (int32) or NULL                      */
+  const void* personalization_values;      /* value_type                                        */
+  uint64_t personalization_size;
+  int64_t fixed_iterations;            /* > 0: run exactly this many iterations, no stop test
+                                          (parity at an identical iteration count; benchmarks)  */
+} b200_pagerank_params_t;
+
+/* cugraph::pagerank (cpp/include/cugraph/algorithms.hpp:1147-1159; driver
+ * cpp/src/link_analysis/pagerank_impl.cuh:48-293).  pageranks: value_type[local V] (device),
+ * internal order.  Returns CUGRAPH_UNKNOWN_ERROR with "PageRank failed to converge." exactly
+ * where the reference throws (pagerank_impl.cuh:287-291). */
+int b200_pagerank(b200_handle_t* h, b200_graph_t* g, const b200_pagerank_params_t* p,
+                  void* pageranks, b200_centrality_stats_t* stats);
+
+typedef struct b200_katz_params {
+  double alpha;
+  double beta;
+  double epsilon;
+  uint64_t max_iterations;
+  int32_t value_type;
+  int32_t has_initial_guess;
+  int32_t normalize;
+  const void* betas; /* value_type[local V] or NULL */
+  int64_t fixed_iterations;
+} b200_katz_params_t;
+
+/* cugraph::katz_centrality (algorithms.hpp:1272-1283; katz_centrality_impl.cuh:42-173) */
+int b200_katz_centrality(b200_handle_t* h, b200_graph_t* g, const b200_katz_params_t* p,
+                         void* centralities, b200_centrality_stats_t* stats);
+
+typedef struct b200_eigenvector_params {
+  double epsilon;
+  uint64_t max_iterations;
+  int32_t value_type;
+  int32_t has_initial_guess;
+  int64_t fixed_iterations;
+} b200_eigenvector_params_t;
+
+/* cugraph::eigenvector_centrality (algorithms.hpp:1187; eigenvector_centrality_impl.cuh:45-138) */
+int b200_eigenvector_centrality(b200_handle_t* h, b200_graph_t* g,
+                                const b200_eigenvector_params_t* p, void* centralities,
+                                b200_centrality_stats_t* stats);
+
+/* -------------------------------------------------------------------------------------------
+ * R-MAT generator — cugraph::generate_rmat_edgelist
+ * (cpp/src/generators/generate_rmat_edgelist.cu:35-111).  Edges [first_edge, first_edge +
+ * num_edges) of the stream identified by seed; ids are int32 (scale <= 31) or int64.
+ * The random stream is this library's counter-based generator, not raft's (parity unpinned,
+ * SURVEY.md 8c); the bit loop is the reference's.
+ * ------------------------------------------------------------------------------------------- */
+int b200_generate_rmat_edgelist(b200_handle_t* h, int scale, size_t num_edges, double a, double b,
+                                double c, uint64_t seed, int clip_and_flip, uint64_t first_edge,
+                                int vertex_type, void* src, void* dst);
+/* uniform [0,1) edge weights from the same generator (test_graphs.hpp:279-284) */
+int b200_uniform_fill(b200_handle_t* h, int value_type, void* out, size_t n, uint64_t seed);
+
+/* library identification: "sm_100a" build tag + version */
+const char* b200_build_info(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_CUGRAPH_H */
