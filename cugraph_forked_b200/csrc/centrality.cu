@@ -1,0 +1,792 @@
+// Power-iteration drivers on top of the pull kernel (spmv.cuh):
+//   PageRank     cpp/src/link_analysis/pagerank_impl.cuh:48-293
+//   Katz         cpp/src/centrality/katz_centrality_impl.cuh:42-173
+//   eigenvector  cpp/src/centrality/eigenvector_centrality_impl.cuh:45-138
+// One SpMV launch + one tail launch per iteration; dangling mass, L1 difference and the stop
+// test live on the device (iter_state), the host only polls the state every few iterations
+// instead of synchronising twice per iteration as the reference does (pagerank_impl.cuh:218,278).
+#include <cmath>
+#include <cstdlib>
+
+#include "centrality.cuh"
+#include "spmv.cuh"
+
+namespace b200 {
+
+namespace {
+
+constexpr int kVThreads = 256;
+
+inline unsigned vgrid(size_t n, int sm_count)
+{
+  size_t b = (n + kVThreads * 4 - 1) / (kVThreads * 4);
+  size_t cap = static_cast<size_t>(sm_count) * 8;
+  if (b > cap) b = cap;
+  if (b == 0) b = 1;
+  return static_cast<unsigned>(b);
+}
+
+// ---- kernel configurations -----------------------------------------------------------------
+template <int T_, int THREADS_, int STAGES_, int CTAS_>
+struct pull_cfg {
+  static constexpr int T       = T_;
+  static constexpr int THREADS = THREADS_;
+  static constexpr int STAGES  = STAGES_;
+  static constexpr int CTAS    = CTAS_;
+};
+// 4-byte results: products overwrite the staged indices in place
+using cfg_f32_default = pull_cfg<4096, 512, 3, 2>;
+// 8-byte results: separate double-buffered product array
+using cfg_f64_default = pull_cfg<2048, 512, 3, 2>;
+
+template <typename RT>
+struct default_cfg {
+  using type = cfg_f32_default;
+};
+template <>
+struct default_cfg<double> {
+  using type = cfg_f64_default;
+};
+
+int env_int(const char* name, int dflt)
+{
+  const char* v = std::getenv(name);
+  return v ? std::atoi(v) : dflt;
+}
+
+// fallback for graphs without degree segments (renumber = false): one warp per row straight
+// from global memory (what the reference does with its low-degree kernel over all vertices,
+// per_v...cuh:814-828, but warp- instead of thread-per-row)
+template <typename ET, typename RT, bool WEIGHTED, typename EPI>
+__global__ void __launch_bounds__(256) pull_rows_generic_kernel(const ET* offsets,
+                                                                const int32_t* indices,
+                                                                const RT* weights, const RT* x,
+                                                                int64_t num_rows, EPI epi,
+                                                                const iter_state* state,
+                                                                double* cta_partials, int slots)
+{
+  __shared__ double red_scratch[32];
+  if (state && state->done) return;
+  epi.setup(state);
+  acc2 acc;
+  const int lane      = threadIdx.x & 31;
+  const int64_t warp  = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5;
+  const int64_t nwarp = (int64_t(gridDim.x) * blockDim.x) >> 5;
+  for (int64_t r = warp; r < num_rows; r += nwarp) {
+    int64_t b = offsets[r], e = offsets[r + 1];
+    RT sum = RT(0);
+    for (int64_t i = b + lane; i < e; i += 32) {
+      RT v = __ldg(x + indices[i]);
+      if (WEIGHTED) v *= weights[i];
+      sum += v;
+    }
+    sum = warp_sum(sum);
+    if (lane == 0) epi(r, sum, acc);
+  }
+  if (cta_partials) {
+    double a = block_sum(acc.a, red_scratch);
+    double b = block_sum(acc.b, red_scratch);
+    if (threadIdx.x == 0) {
+      cta_partials[blockIdx.x]         = a;
+      cta_partials[slots + blockIdx.x] = b;
+    }
+  }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------
+// pull_launcher: everything needed to launch one SpMV (+ tail) over one edge partition
+// ------------------------------------------------------------------------------------------
+template <typename RT>
+struct pull_launcher {
+  b200_handle* h;
+  edge_partition* ep;
+  bool weighted;
+  const RT* weights;  // RT-typed (converted copy if the graph stores another type)
+  dbuf<char> weights_converted;
+  dbuf<double> chunk_partials;
+  dbuf<double> cta_partials;
+  int main_ctas{0};
+  int tail_ctas{1};
+  int slots{0};
+  int T{0};
+  bool tiled{false};
+  int64_t launches{0};
+
+  void init(b200_handle* h_, b200_graph* g, edge_partition* ep_);
+
+  template <typename EPI>
+  void spmv(const RT* x, EPI const& epi, const iter_state* state, bool want_partials);
+  template <typename EPI>
+  void tail(EPI const& epi, iter_state* state, double epsilon, int64_t iteration, bool check,
+            bool finalize);
+};
+
+namespace {
+template <typename A, typename B>
+__global__ void convert_kernel(const A* in, B* out, size_t n)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    out[i] = static_cast<B>(in[i]);
+}
+}  // namespace
+
+template <typename RT>
+void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_)
+{
+  using CFG = typename default_cfg<RT>::type;
+  h         = h_;
+  ep        = ep_;
+  weighted  = g->weighted;
+  weights   = nullptr;
+  cudaStream_t s = h->stream;
+  if (weighted) {
+    int want = sizeof(RT) == 4 ? B200_FLOAT32 : B200_FLOAT64;
+    if (g->weight_type == want) {
+      weights = reinterpret_cast<const RT*>(ep->weights.data());
+    } else {
+      size_t ne = static_cast<size_t>(ep->num_edges);
+      weights_converted.alloc(ne * sizeof(RT), s, 32);
+      if (ne) {
+        if (g->weight_type == B200_FLOAT32)
+          convert_kernel<float, RT><<<vgrid(ne, h->sm_count), kVThreads, 0, s>>>(
+            reinterpret_cast<const float*>(ep->weights.data()),
+            reinterpret_cast<RT*>(weights_converted.data()), ne);
+        else
+          convert_kernel<double, RT><<<vgrid(ne, h->sm_count), kVThreads, 0, s>>>(
+            reinterpret_cast<const double*>(ep->weights.data()),
+            reinterpret_cast<RT*>(weights_converted.data()), ne);
+        CUDA_TRY(cudaGetLastError());
+      }
+      weights = reinterpret_cast<const RT*>(weights_converted.data());
+    }
+  }
+  tiled = ep->has_segments;
+  T     = CFG::T;
+  if (tiled) {
+    build_schedule(h, *ep, T);
+    main_ctas = CFG::CTAS * h->sm_count;
+    if (ep->num_tiles < main_ctas) main_ctas = static_cast<int>(std::max<int64_t>(ep->num_tiles, 1));
+    int64_t want_tail = div_up(std::max<int64_t>(ep->num_long_rows, 1), 8);
+    tail_ctas         = static_cast<int>(std::min<int64_t>(want_tail, 64));
+  } else {
+    main_ctas = h->sm_count * 8;
+    tail_ctas = 1;
+  }
+  slots = main_ctas + tail_ctas;
+  chunk_partials.alloc(static_cast<size_t>(std::max<int64_t>(ep->num_chunks, 1)), s);
+  cta_partials.alloc(static_cast<size_t>(2 * slots), s);
+  CUDA_TRY(cudaMemsetAsync(cta_partials.data(), 0, sizeof(double) * 2 * slots, s));
+}
+
+template <typename RT>
+template <typename EPI>
+void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* state,
+                             bool want_partials)
+{
+  using CFG      = typename default_cfg<RT>::type;
+  cudaStream_t s = h->stream;
+  double* parts  = want_partials ? cta_partials.data() : nullptr;
+  if (!tiled) {
+    auto go = [&](auto et, auto wtag) {
+      using ET            = decltype(et);
+      constexpr bool W    = decltype(wtag)::value;
+      pull_rows_generic_kernel<ET, RT, W, EPI><<<main_ctas, 256, 0, s>>>(
+        reinterpret_cast<const ET*>(ep->offsets.data()), ep->indices.data(), weights, x,
+        ep->num_rows, epi, state, parts, slots);
+    };
+    if (ep->offsets64) {
+      if (weighted) go(int64_t{}, std::true_type{}); else go(int64_t{}, std::false_type{});
+    } else {
+      if (weighted) go(int32_t{}, std::true_type{}); else go(int32_t{}, std::false_type{});
+    }
+    CUDA_TRY(cudaGetLastError());
+    ++launches;
+    return;
+  }
+  pull_params P{};
+  P.tiles          = ep->tiles.data();
+  P.num_tiles      = ep->num_tiles;
+  P.offsets        = ep->offsets.data();
+  P.indices        = ep->indices.data();
+  P.weights        = weights;
+  P.x              = x;
+  P.zero_first     = ep->seg[3];
+  P.num_rows       = ep->num_rows;
+  P.chunk_partials = chunk_partials.data();
+  P.cta_partials   = parts;
+  P.slots          = slots;
+  P.state          = state;
+  auto go = [&](auto et, auto wtag) {
+    using ET         = decltype(et);
+    constexpr bool W = decltype(wtag)::value;
+    using SM         = pull_smem<ET, RT, RT, W, CFG::T, CFG::STAGES>;
+    auto kern = pull_tiles_kernel<ET, RT, RT, W, EPI, CFG::T, CFG::THREADS, CFG::STAGES, CFG::CTAS>;
+    static bool configured = false;
+    if (!configured) {
+      CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    static_cast<int>(SM::total)));
+      configured = true;
+    }
+    kern<<<main_ctas, CFG::THREADS, SM::total, s>>>(P, epi);
+  };
+  if (ep->offsets64) {
+    if (weighted) go(int64_t{}, std::true_type{}); else go(int64_t{}, std::false_type{});
+  } else {
+    if (weighted) go(int32_t{}, std::true_type{}); else go(int32_t{}, std::false_type{});
+  }
+  CUDA_TRY(cudaGetLastError());
+  ++launches;
+}
+
+template <typename RT>
+template <typename EPI>
+void pull_launcher<RT>::tail(EPI const& epi, iter_state* state, double epsilon, int64_t iteration,
+                             bool check, bool finalize)
+{
+  tail_params P{};
+  P.long_row_chunk_first = tiled ? ep->long_row_chunk_first.data() : nullptr;
+  P.chunk_partials       = chunk_partials.data();
+  P.num_long_rows        = tiled ? ep->num_long_rows : 0;
+  P.cta_partials         = finalize ? cta_partials.data() : nullptr;
+  P.slots                = slots;
+  P.main_ctas            = main_ctas;
+  P.state                = state;
+  P.epsilon              = epsilon;
+  P.iteration            = iteration;
+  P.check_convergence    = check ? 1 : 0;
+  P.finalize             = finalize ? 1 : 0;
+  if (!finalize && P.num_long_rows == 0) return;
+  pull_tail_kernel<RT, EPI, 256><<<tail_ctas, 256, 0, h->stream>>>(P, epi);
+  CUDA_TRY(cudaGetLastError());
+  ++launches;
+}
+
+// ------------------------------------------------------------------------------------------
+// vertex passes (replace the thrust::transform / transform_reduce_v calls of the drivers)
+// ------------------------------------------------------------------------------------------
+namespace {
+
+// per-block partial sums -> slots; the finalize kernel folds them in a fixed order
+template <typename RT>
+__global__ void __launch_bounds__(kVThreads) sum_kernel(const RT* v, size_t n, double* partials)
+{
+  __shared__ double scratch[32];
+  double s = 0.0;
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    s += static_cast<double>(v[i]);
+  s = block_sum(s, scratch);
+  if (threadIdx.x == 0) partials[blockIdx.x] = s;
+}
+
+// state->a = sum(pa[0..n)), state->b = sum(pb[0..n)) (either may be nullptr)
+__global__ void __launch_bounds__(256) fold_kernel(const double* pa, const double* pb, int n,
+                                                   iter_state* st)
+{
+  __shared__ double scratch[32];
+  double a = 0.0, b = 0.0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    if (pa) a += pa[i];
+    if (pb) b += pb[i];
+  }
+  a = block_sum(a, scratch);
+  b = block_sum(b, scratch);
+  if (threadIdx.x == 0) {
+    if (pa) st->a = a;
+    if (pb) st->b = b;
+  }
+}
+
+// scale[v] = alpha / out_weight[v], or -1 when out_weight[v] == 0 (dangling)
+template <typename RT, typename WT>
+__global__ void __launch_bounds__(kVThreads) pagerank_scale_kernel(const WT* outw, size_t n,
+                                                                  RT alpha, RT* scale)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    RT w     = static_cast<RT>(outw[i]);
+    scale[i] = (w == RT(0)) ? RT(-1) : alpha / w;
+  }
+}
+
+// pr = guess / sum (or 1/V); x0 = pr * scale; dangling partials
+template <typename RT>
+__global__ void __launch_bounds__(kVThreads) pagerank_init_kernel(RT* pr, const RT* scale, RT* x0,
+                                                                 size_t n, int has_guess,
+                                                                 const iter_state* st, RT uniform,
+                                                                 double* partials)
+{
+  __shared__ double scratch[32];
+  double dang = 0.0;
+  RT sum      = has_guess ? static_cast<RT>(st->a) : RT(1);
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    RT v  = has_guess ? pr[i] / sum : uniform;
+    pr[i] = v;
+    RT sc = scale[i];
+    if (sc < RT(0)) {
+      dang += static_cast<double>(v);
+      x0[i] = RT(0);
+    } else {
+      x0[i] = v * sc;
+    }
+  }
+  dang = block_sum(dang, scratch);
+  if (threadIdx.x == 0) partials[blockIdx.x] = dang;
+}
+
+template <typename RT>
+__global__ void __launch_bounds__(kVThreads) scatter_pers_kernel(const int32_t* vertices,
+                                                                const RT* values, size_t n,
+                                                                RT pers_sum, int64_t first,
+                                                                int64_t nv, RT* dense, int* bad)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    int64_t v = static_cast<int64_t>(vertices[i]) - first;
+    if (v < 0 || v >= nv) { *bad = 1; continue; }
+    // duplicates accumulate, as the reference's per-entry += does (pagerank_impl.cuh:259-276)
+    atomicAdd(&dense[v], values[i] / pers_sum);
+  }
+}
+
+template <typename RT>
+__global__ void __launch_bounds__(kVThreads) divide_kernel(RT* v, size_t n, RT d)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    v[i] = v[i] / d;
+}
+
+template <typename RT>
+__global__ void __launch_bounds__(kVThreads) fill_kernel(RT* v, size_t n, RT x)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    v[i] = x;
+}
+
+// eigenvector: c = c / norm, diff partial = |c - old|
+template <typename RT>
+__global__ void __launch_bounds__(kVThreads) eigen_normalize_kernel(RT* c, const RT* old, size_t n,
+                                                                   const iter_state* st,
+                                                                   double* partials)
+{
+  __shared__ double scratch[32];
+  if (st->done) return;
+  RT norm     = static_cast<RT>(sqrt(st->a));
+  double diff = 0.0;
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    RT v = c[i] / norm;
+    c[i] = v;
+    diff += fabs(static_cast<double>(v) - static_cast<double>(old[i]));
+  }
+  diff = block_sum(diff, scratch);
+  if (threadIdx.x == 0) partials[blockIdx.x] = diff;
+}
+
+// fold diff partials, stop test, iteration bookkeeping (eigenvector)
+__global__ void __launch_bounds__(256) eigen_fold_kernel(const double* partials, int n,
+                                                         iter_state* st, double threshold,
+                                                         int64_t iteration, int check)
+{
+  __shared__ double scratch[32];
+  if (st->done) return;
+  double b = 0.0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) b += partials[i];
+  b = block_sum(b, scratch);
+  if (threadIdx.x == 0) {
+    st->b          = b;
+    st->iterations = iteration;
+    if (check && b < threshold) {
+      st->converged = 1;
+      st->done      = 1;
+    }
+  }
+}
+
+struct host_state {
+  iter_state st;
+};
+
+void read_state(b200_handle* h, const iter_state* d, iter_state* out)
+{
+  CUDA_TRY(cudaMemcpyAsync(out, d, sizeof(iter_state), cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+}
+
+struct loop_timer {
+  cudaEvent_t e0{}, e1{};
+  cudaStream_t s;
+  explicit loop_timer(cudaStream_t s_) : s(s_)
+  {
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+  }
+  ~loop_timer()
+  {
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+  }
+  void start() { cudaEventRecord(e0, s); }
+  double stop()
+  {
+    cudaEventRecord(e1, s);
+    cudaEventSynchronize(e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    return ms;
+  }
+};
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------
+// PageRank (single GPU)
+// ------------------------------------------------------------------------------------------
+template <typename RT>
+static void pagerank_sg(b200_handle* h, b200_graph* g, const b200_pagerank_params_t* p, RT* pr,
+                        b200_centrality_stats_t* stats)
+{
+  cudaStream_t s    = h->stream;
+  const int64_t nv  = g->num_vertices;
+  const size_t n    = static_cast<size_t>(nv);
+  const RT alpha    = static_cast<RT>(p->alpha);
+  const RT epsilon  = static_cast<RT>(p->epsilon);
+  const bool fixed  = p->fixed_iterations > 0;
+  const int64_t cap = fixed ? p->fixed_iterations
+                            : std::max<int64_t>(1, static_cast<int64_t>(p->max_iterations));
+  if (stats) *stats = b200_centrality_stats_t{};
+  if (nv == 0) return;
+
+  pull_launcher<RT> L;
+  L.init(h, g, &g->parts[0]);
+  const unsigned vg = vgrid(n, h->sm_count);
+
+  dbuf<iter_state> d_state(1, s);
+  CUDA_TRY(cudaMemsetAsync(d_state.data(), 0, sizeof(iter_state), s));
+  dbuf<double> vparts(vg, s);
+
+  // out-weight sums -> scale
+  dbuf<RT> scale(n, s);
+  if (p->precomputed_out_weight_sums) {
+    pagerank_scale_kernel<RT, RT><<<vg, kVThreads, 0, s>>>(
+      static_cast<const RT*>(p->precomputed_out_weight_sums), n, alpha, scale.data());
+  } else {
+    graph_out_weight_sums(h, g);
+    // the reference holds the sums in weight_t (graph_view_impl.cuh:238-265); round the same way
+    pagerank_scale_kernel<RT, double><<<vg, kVThreads, 0, s>>>(g->out_weight_sums.data(), n, alpha,
+                                                              scale.data());
+  }
+  CUDA_TRY(cudaGetLastError());
+
+  // personalization (dense, normalised)
+  dbuf<RT> pers;
+  const bool personalized = p->personalization_vertices != nullptr && p->personalization_size > 0;
+  if (p->personalization_vertices != nullptr) {
+    B200_EXPECTS(p->personalization_values != nullptr, kInvalidInput,
+                 "Invalid input argument: if personalization_vertices.has_value() is true, "
+                 "personalization_values.has_value() and personalization_vector_size.has_value() "
+                 "should be true as well.");
+  }
+  if (personalized) {
+    size_t np   = static_cast<size_t>(p->personalization_size);
+    unsigned pg = vgrid(np, h->sm_count);
+    dbuf<double> pparts(pg, s);
+    sum_kernel<RT><<<pg, kVThreads, 0, s>>>(static_cast<const RT*>(p->personalization_values), np,
+                                            pparts.data());
+    fold_kernel<<<1, 256, 0, s>>>(pparts.data(), nullptr, static_cast<int>(pg), d_state.data());
+    CUDA_TRY(cudaGetLastError());
+    iter_state hs;
+    read_state(h, d_state.data(), &hs);
+    RT pers_sum = static_cast<RT>(hs.a);
+    B200_EXPECTS(pers_sum > RT(0), kInvalidInput,
+                 "Invalid input argument: sum of personalization valuese should be positive.");
+    pers.alloc(n, s);
+    CUDA_TRY(cudaMemsetAsync(pers.data(), 0, n * sizeof(RT), s));
+    dbuf<int> bad(1, s);
+    CUDA_TRY(cudaMemsetAsync(bad.data(), 0, 4, s));
+    scatter_pers_kernel<RT><<<pg, kVThreads, 0, s>>>(
+      static_cast<const int32_t*>(p->personalization_vertices),
+      static_cast<const RT*>(p->personalization_values), np, pers_sum, 0, nv, pers.data(),
+      bad.data());
+    CUDA_TRY(cudaGetLastError());
+    int h_bad = 0;
+    CUDA_TRY(cudaMemcpyAsync(&h_bad, bad.data(), 4, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    B200_EXPECTS(!h_bad, kInvalidInput,
+                 "Invalid input argument: peresonalization vertices have invalid vertex IDs.");
+  }
+
+  // initial values
+  if (p->has_initial_guess) {
+    sum_kernel<RT><<<vg, kVThreads, 0, s>>>(pr, n, vparts.data());
+    fold_kernel<<<1, 256, 0, s>>>(vparts.data(), nullptr, static_cast<int>(vg), d_state.data());
+    CUDA_TRY(cudaGetLastError());
+    iter_state hs;
+    read_state(h, d_state.data(), &hs);
+    B200_EXPECTS(static_cast<RT>(hs.a) > RT(0), kInvalidInput,
+                 "Invalid input argument: sum of the PageRank initial guess values should be "
+                 "positive.");
+  }
+  dbuf<RT> xbuf(2 * n, s);
+  RT* x[2] = {xbuf.data(), xbuf.data() + n};
+  pagerank_init_kernel<RT><<<vg, kVThreads, 0, s>>>(pr, scale.data(), x[0], n,
+                                                    p->has_initial_guess ? 1 : 0, d_state.data(),
+                                                    RT(1) / static_cast<RT>(nv), vparts.data());
+  fold_kernel<<<1, 256, 0, s>>>(vparts.data(), nullptr, static_cast<int>(vg), d_state.data());
+  CUDA_TRY(cudaGetLastError());
+
+  epi_pagerank<RT> epi{};
+  epi.pr                  = pr;
+  epi.scale               = scale.data();
+  epi.pers                = personalized ? pers.data() : nullptr;
+  epi.alpha               = alpha;
+  epi.one_minus_alpha     = static_cast<RT>(1.0 - p->alpha);
+  epi.inv_or_num_vertices = static_cast<RT>(nv);
+
+  const int check_every = std::max(1, env_int("B200_CHECK_EVERY", 8));
+  loop_timer timer(s);
+  timer.start();
+  iter_state hs{};
+  int64_t it = 0;
+  for (; it < cap; ++it) {
+    epi.x_next = x[(it + 1) & 1];
+    L.spmv(x[it & 1], epi, d_state.data(), true);
+    L.tail(epi, d_state.data(), static_cast<double>(epsilon), it + 1, !fixed, true);
+    if (!fixed && ((it + 1) % check_every == 0)) {
+      read_state(h, d_state.data(), &hs);
+      if (hs.done) break;
+    }
+  }
+  double ms = timer.stop();
+  read_state(h, d_state.data(), &hs);
+  if (stats) {
+    stats->iterations   = hs.iterations;
+    stats->converged    = hs.converged;
+    stats->last_diff    = hs.b;
+    stats->elapsed_ms   = ms;
+    stats->gpu_launches = L.launches;
+  }
+  if (!fixed && !hs.converged) {
+    throw error(kUnknownError, "PageRank failed to converge.");
+  }
+}
+
+void pagerank(b200_handle* h, b200_graph* g, const b200_pagerank_params_t* p, void* pageranks,
+              b200_centrality_stats_t* stats)
+{
+  B200_EXPECTS(g->store_transposed, kInvalidInput,
+               "PageRank needs a graph stored transposed (pull layout).");
+  B200_EXPECTS((p->alpha >= 0.0) && (p->alpha <= 1.0), kInvalidInput,
+               "Invalid input argument: alpha should be in [0.0, 1.0].");
+  B200_EXPECTS(p->epsilon >= 0.0, kInvalidInput,
+               "Invalid input argument: epsilon should be non-negative.");
+  B200_EXPECTS(p->value_type == B200_FLOAT32 || p->value_type == B200_FLOAT64,
+               kUnsupportedTypeCombination, "result type must be FLOAT32 or FLOAT64");
+  if (g->multi_gpu) {
+    pagerank_mg(h, g, p, pageranks, stats);
+    return;
+  }
+  if (p->value_type == B200_FLOAT32)
+    pagerank_sg<float>(h, g, p, static_cast<float*>(pageranks), stats);
+  else
+    pagerank_sg<double>(h, g, p, static_cast<double*>(pageranks), stats);
+}
+
+// ------------------------------------------------------------------------------------------
+// Katz centrality (single GPU)
+// ------------------------------------------------------------------------------------------
+template <typename RT>
+static void katz_sg(b200_handle* h, b200_graph* g, const b200_katz_params_t* p, RT* kc,
+                    b200_centrality_stats_t* stats)
+{
+  cudaStream_t s    = h->stream;
+  const int64_t nv  = g->num_vertices;
+  const size_t n    = static_cast<size_t>(nv);
+  const bool fixed  = p->fixed_iterations > 0;
+  const int64_t cap = fixed ? p->fixed_iterations
+                            : std::max<int64_t>(1, static_cast<int64_t>(p->max_iterations));
+  const RT epsilon  = static_cast<RT>(p->epsilon);
+  if (stats) *stats = b200_centrality_stats_t{};
+  if (nv == 0) return;
+
+  pull_launcher<RT> L;
+  L.init(h, g, &g->parts[0]);
+  const unsigned vg = vgrid(n, h->sm_count);
+  dbuf<iter_state> d_state(1, s);
+  CUDA_TRY(cudaMemsetAsync(d_state.data(), 0, sizeof(iter_state), s));
+  if (!p->has_initial_guess) CUDA_TRY(cudaMemsetAsync(kc, 0, n * sizeof(RT), s));
+  dbuf<RT> tmp(n, s);
+  // buffers alternate; iteration `it` reads buf[it & 1] and writes buf[(it + 1) & 1]
+  RT* buf[2] = {kc, tmp.data()};
+
+  epi_katz<RT> epi{};
+  epi.betas = static_cast<const RT*>(p->betas);
+  epi.alpha = static_cast<RT>(p->alpha);
+  epi.beta  = static_cast<RT>(p->beta);
+
+  const int check_every = std::max(1, env_int("B200_CHECK_EVERY", 8));
+  loop_timer timer(s);
+  timer.start();
+  iter_state hs{};
+  for (int64_t it = 0; it < cap; ++it) {
+    epi.old_c = buf[it & 1];
+    epi.new_c = buf[(it + 1) & 1];
+    L.spmv(epi.old_c, epi, d_state.data(), true);
+    L.tail(epi, d_state.data(), static_cast<double>(epsilon), it + 1, !fixed, true);
+    if (!fixed && ((it + 1) % check_every == 0)) {
+      read_state(h, d_state.data(), &hs);
+      if (hs.done) break;
+    }
+  }
+  double ms = timer.stop();
+  read_state(h, d_state.data(), &hs);
+  if (stats) {
+    stats->iterations   = hs.iterations;
+    stats->converged    = hs.converged;
+    stats->last_diff    = hs.b;
+    stats->elapsed_ms   = ms;
+    stats->gpu_launches = L.launches;
+  }
+  if (!fixed && !hs.converged) throw error(kUnknownError, "Katz Centrality failed to converge.");
+  RT* result = buf[hs.iterations & 1];
+  if (result != kc)
+    CUDA_TRY(cudaMemcpyAsync(kc, result, n * sizeof(RT), cudaMemcpyDeviceToDevice, s));
+  if (p->normalize) {
+    RT l2 = static_cast<RT>(std::sqrt(static_cast<RT>(hs.a)));
+    B200_EXPECTS(l2 > RT(0), kUnknownError,
+                 "L2 norm of the computed Katz Centrality values should be positive.");
+    divide_kernel<RT><<<vg, kVThreads, 0, s>>>(kc, n, l2);
+    CUDA_TRY(cudaGetLastError());
+  }
+  CUDA_TRY(cudaStreamSynchronize(s));
+}
+
+void katz_centrality(b200_handle* h, b200_graph* g, const b200_katz_params_t* p, void* out,
+                     b200_centrality_stats_t* stats)
+{
+  B200_EXPECTS(g->store_transposed, kInvalidInput,
+               "Katz centrality needs a graph stored transposed (pull layout).");
+  B200_EXPECTS((p->alpha >= 0.0) && (p->alpha <= 1.0), kInvalidInput,
+               "Invalid input argument: alpha should be in [0.0, 1.0].");
+  B200_EXPECTS(p->epsilon >= 0.0, kInvalidInput,
+               "Invalid input argument: epsilon should be non-negative.");
+  if (g->multi_gpu) {
+    katz_mg(h, g, p, out, stats);
+    return;
+  }
+  if (p->value_type == B200_FLOAT32) katz_sg<float>(h, g, p, static_cast<float*>(out), stats);
+  else katz_sg<double>(h, g, p, static_cast<double*>(out), stats);
+}
+
+// ------------------------------------------------------------------------------------------
+// eigenvector centrality (single GPU)
+// ------------------------------------------------------------------------------------------
+template <typename RT>
+static void eigen_sg(b200_handle* h, b200_graph* g, const b200_eigenvector_params_t* p, RT* c,
+                     b200_centrality_stats_t* stats)
+{
+  cudaStream_t s    = h->stream;
+  const int64_t nv  = g->num_vertices;
+  const size_t n    = static_cast<size_t>(nv);
+  const bool fixed  = p->fixed_iterations > 0;
+  const int64_t cap = fixed ? p->fixed_iterations
+                            : std::max<int64_t>(1, static_cast<int64_t>(p->max_iterations));
+  if (stats) *stats = b200_centrality_stats_t{};
+  if (nv == 0) return;
+  pull_launcher<RT> L;
+  L.init(h, g, &g->parts[0]);
+  const unsigned vg = vgrid(n, h->sm_count);
+  dbuf<iter_state> d_state(1, s);
+  CUDA_TRY(cudaMemsetAsync(d_state.data(), 0, sizeof(iter_state), s));
+  dbuf<double> vparts(vg, s);
+  dbuf<RT> tmp(n, s);
+  if (!p->has_initial_guess) {
+    fill_kernel<RT><<<vg, kVThreads, 0, s>>>(c, n, RT(1) / static_cast<RT>(nv));
+    CUDA_TRY(cudaGetLastError());
+  }
+  RT* buf[2] = {c, tmp.data()};
+  epi_eigen<RT> epi{};
+  // the reference compares against number_of_vertices * epsilon in weight_t arithmetic
+  const double threshold = static_cast<double>(static_cast<RT>(nv) * static_cast<RT>(p->epsilon));
+  const int check_every  = std::max(1, env_int("B200_CHECK_EVERY", 8));
+  loop_timer timer(s);
+  timer.start();
+  iter_state hs{};
+  int64_t extra = 0;
+  for (int64_t it = 0; it < cap; ++it) {
+    RT* old_c = buf[it & 1];
+    epi.new_c = buf[(it + 1) & 1];
+    L.spmv(old_c, epi, d_state.data(), true);
+    // tail folds sum of squares into state.a (no stop test here)
+    L.tail(epi, d_state.data(), 0.0, it, false, true);
+    eigen_normalize_kernel<RT><<<vg, kVThreads, 0, s>>>(epi.new_c, old_c, n, d_state.data(),
+                                                        vparts.data());
+    eigen_fold_kernel<<<1, 256, 0, s>>>(vparts.data(), static_cast<int>(vg), d_state.data(),
+                                        threshold, it + 1, fixed ? 0 : 1);
+    CUDA_TRY(cudaGetLastError());
+    extra += 2;
+    if (!fixed && ((it + 1) % check_every == 0)) {
+      read_state(h, d_state.data(), &hs);
+      if (hs.done) break;
+    }
+  }
+  double ms = timer.stop();
+  read_state(h, d_state.data(), &hs);
+  if (stats) {
+    stats->iterations   = hs.iterations;
+    stats->converged    = hs.converged;
+    stats->last_diff    = hs.b;
+    stats->elapsed_ms   = ms;
+    stats->gpu_launches = L.launches + extra;
+  }
+  if (!fixed && !hs.converged)
+    throw error(kUnknownError, "Eigenvector Centrality failed to converge.");
+  RT* result = buf[hs.iterations & 1];
+  if (result != c) CUDA_TRY(cudaMemcpyAsync(c, result, n * sizeof(RT), cudaMemcpyDeviceToDevice, s));
+  CUDA_TRY(cudaStreamSynchronize(s));
+}
+
+void eigenvector_centrality(b200_handle* h, b200_graph* g, const b200_eigenvector_params_t* p,
+                            void* out, b200_centrality_stats_t* stats)
+{
+  B200_EXPECTS(g->store_transposed, kInvalidInput,
+               "Eigenvector centrality needs a graph stored transposed (pull layout).");
+  B200_EXPECTS(p->epsilon >= 0.0, kInvalidInput,
+               "Invalid input argument: epsilon should be non-negative.");
+  B200_EXPECTS(!g->multi_gpu, kNotImplemented, "multi-GPU eigenvector centrality");
+  if (p->value_type == B200_FLOAT32) eigen_sg<float>(h, g, p, static_cast<float*>(out), stats);
+  else eigen_sg<double>(h, g, p, static_cast<double*>(out), stats);
+}
+
+// ------------------------------------------------------------------------------------------
+// raw SpMV: y = init + scale * A^T x
+// ------------------------------------------------------------------------------------------
+template <typename RT>
+static void spmv_sg(b200_handle* h, b200_graph* g, const RT* x, double scale, double init, RT* y)
+{
+  if (g->num_vertices == 0) return;
+  pull_launcher<RT> L;
+  L.init(h, g, &g->parts[0]);
+  epi_raw<RT> epi{y, static_cast<RT>(scale), static_cast<RT>(init)};
+  L.spmv(x, epi, nullptr, false);
+  L.tail(epi, nullptr, 0.0, 0, false, false);
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+}
+
+void spmv_pull(b200_handle* h, b200_graph* g, int value_type, const void* x, double scale,
+               double init, void* y)
+{
+  B200_EXPECTS(!g->multi_gpu, kNotImplemented, "b200_spmv_pull is single-GPU");
+  if (value_type == B200_FLOAT32)
+    spmv_sg<float>(h, g, static_cast<const float*>(x), scale, init, static_cast<float*>(y));
+  else
+    spmv_sg<double>(h, g, static_cast<const double*>(x), scale, init, static_cast<double*>(y));
+}
+
+}  // namespace b200

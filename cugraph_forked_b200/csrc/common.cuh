@@ -37,6 +37,9 @@ struct error : std::runtime_error {
 
 void set_last_error(const char* msg);
 
+#define B200_STR2(x) #x
+#define B200_STR(x) B200_STR2(x)
+
 #define B200_EXPECTS(cond, code, msg)                 \
   do {                                                \
     if (!(cond)) throw ::b200::error((code), (msg));  \

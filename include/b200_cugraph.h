@@ -3,7 +3,7 @@
  *
  * This is the boundary a libcugraph maintainer binds: plain pointers and sizes, no C++ or
  * torch types.  Every entry point names the reference interface it stands in for (paths are
- * relative to the reference tree).  The cugraph_c-compatible layer (include/cugraph_c/*.h,
+ * relative to the reference tree).  The cugraph_c-compatible layer (the headers under include/cugraph_c,
  * cugraph_forked_b200/csrc/c_api.cu) and the Python mirror of pylibcugraph both sit on top
  * of exactly these calls.
  *
