@@ -27,27 +27,27 @@ inline unsigned vgrid(size_t n, int sm_count)
 }
 
 // ---- kernel configurations -----------------------------------------------------------------
-template <int T_, int THREADS_, int STAGES_, int CTAS_>
+template <int T_, int STAGES_>
 struct pull_cfg {
-  static constexpr int T       = T_;
-  static constexpr int THREADS = THREADS_;
-  static constexpr int STAGES  = STAGES_;
-  static constexpr int CTAS    = CTAS_;
+  static constexpr int T      = T_;
+  static constexpr int STAGES = STAGES_;
 };
-// 4-byte results: products overwrite the staged indices in place
-using cfg_f32_default = pull_cfg<4096, 512, 3, 2>;
-// 8-byte results: separate double-buffered product array
-using cfg_f64_default = pull_cfg<2048, 512, 3, 2>;
-
-template <typename RT>
+template <typename RT, bool WEIGHTED>
 struct default_cfg {
-  using type = cfg_f32_default;
+  using type = pull_cfg<4096, 3>;  // f32 unweighted: 3 x 24.6 KB ring + hub cache
 };
 template <>
-struct default_cfg<double> {
-  using type = cfg_f64_default;
+struct default_cfg<float, true> {
+  using type = pull_cfg<2048, 3>;
 };
-
+template <>
+struct default_cfg<double, false> {
+  using type = pull_cfg<2048, 3>;
+};
+template <>
+struct default_cfg<double, true> {
+  using type = pull_cfg<1024, 3>;
+};
 int env_int(const char* name, int dflt)
 {
   const char* v = std::getenv(name);
@@ -136,7 +136,6 @@ __global__ void convert_kernel(const A* in, B* out, size_t n)
 template <typename RT>
 void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_)
 {
-  using CFG = typename default_cfg<RT>::type;
   h         = h_;
   ep        = ep_;
   weighted  = g->weighted;
@@ -164,10 +163,10 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
     }
   }
   tiled = ep->has_segments;
-  T     = CFG::T;
+  T     = weighted ? default_cfg<RT, true>::type::T : default_cfg<RT, false>::type::T;
   if (tiled) {
     build_schedule(h, *ep, T);
-    main_ctas = CFG::CTAS * h->sm_count;
+    main_ctas = h->sm_count;  // one persistent warp-specialised CTA per SM
     if (ep->num_tiles < main_ctas) main_ctas = static_cast<int>(std::max<int64_t>(ep->num_tiles, 1));
     int64_t want_tail = div_up(std::max<int64_t>(ep->num_long_rows, 1), 8);
     tail_ctas         = static_cast<int>(std::min<int64_t>(want_tail, 64));
@@ -186,7 +185,6 @@ template <typename EPI>
 void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* state,
                              bool want_partials)
 {
-  using CFG      = typename default_cfg<RT>::type;
   cudaStream_t s = h->stream;
   double* parts  = want_partials ? cta_partials.data() : nullptr;
   if (!tiled) {
@@ -219,18 +217,27 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
   P.cta_partials   = parts;
   P.slots          = slots;
   P.state          = state;
+  const int hub_cap = env_int("B200_HUB_ENTRIES", 1 << 30);
   auto go = [&](auto et, auto wtag) {
     using ET         = decltype(et);
     constexpr bool W = decltype(wtag)::value;
-    using SM         = pull_smem<ET, RT, RT, W, CFG::T, CFG::STAGES>;
-    auto kern = pull_tiles_kernel<ET, RT, RT, W, EPI, CFG::T, CFG::THREADS, CFG::STAGES, CFG::CTAS>;
+    using CFG        = typename default_cfg<RT, W>::type;
+    using SM         = pull_smem<ET, RT, W, CFG::T, CFG::STAGES, EPI::kStage>;
+    auto kern        = pull_tiles_kernel<ET, RT, W, EPI, CFG::T, CFG::STAGES>;
+    // the hub cache takes what is left of the shared-memory budget; the budget leaves L1 enough
+    // lines to track the outstanding gathers (profiles/microbench_gather.md)
+    const int64_t budget = static_cast<int64_t>(env_int("B200_SMEM_BUDGET_KB", 160)) * 1024;
+    int64_t room = std::max<int64_t>(0, budget - static_cast<int64_t>(SM::ring)) / sizeof(RT);
+    int hub = static_cast<int>(std::min<int64_t>({ep->num_minors, SM::max_hub, room})) & ~31;
+    hub     = std::max(0, std::min(hub, hub_cap));
     static bool configured = false;
     if (!configured) {
       CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    static_cast<int>(SM::total)));
+                                    static_cast<int>(SM::total(SM::max_hub))));
       configured = true;
     }
-    kern<<<main_ctas, CFG::THREADS, SM::total, s>>>(P, epi);
+    P.hub_entries = hub;
+    kern<<<main_ctas, kPullThreads, SM::total(hub), s>>>(P, epi);
   };
   if (ep->offsets64) {
     if (weighted) go(int64_t{}, std::true_type{}); else go(int64_t{}, std::false_type{});
@@ -472,7 +479,13 @@ static void pagerank_sg(b200_handle* h, b200_graph* g, const b200_pagerank_param
   dbuf<double> vparts(vg, s);
 
   // out-weight sums -> scale
-  dbuf<RT> scale(n, s);
+  // arrays the TMA producer stages by 16-byte pieces are padded past their logical end
+  dbuf<RT> scale(n, s, 8);
+  dbuf<RT> pr_work(n, s, 8);
+  RT* const pr_user = pr;
+  if (p->has_initial_guess)
+    CUDA_TRY(cudaMemcpyAsync(pr_work.data(), pr_user, n * sizeof(RT), cudaMemcpyDeviceToDevice, s));
+  pr = pr_work.data();
   if (p->precomputed_out_weight_sums) {
     pagerank_scale_kernel<RT, RT><<<vg, kVThreads, 0, s>>>(
       static_cast<const RT*>(p->precomputed_out_weight_sums), n, alpha, scale.data());
@@ -547,7 +560,7 @@ static void pagerank_sg(b200_handle* h, b200_graph* g, const b200_pagerank_param
   epi.pers                = personalized ? pers.data() : nullptr;
   epi.alpha               = alpha;
   epi.one_minus_alpha     = static_cast<RT>(1.0 - p->alpha);
-  epi.inv_or_num_vertices = static_cast<RT>(nv);
+  epi.num_vertices        = static_cast<RT>(nv);
 
   const int check_every = std::max(1, env_int("B200_CHECK_EVERY", 8));
   loop_timer timer(s);
@@ -572,6 +585,8 @@ static void pagerank_sg(b200_handle* h, b200_graph* g, const b200_pagerank_param
     stats->elapsed_ms   = ms;
     stats->gpu_launches = L.launches;
   }
+  CUDA_TRY(cudaMemcpyAsync(pr_user, pr, n * sizeof(RT), cudaMemcpyDeviceToDevice, s));
+  CUDA_TRY(cudaStreamSynchronize(s));
   if (!fixed && !hs.converged) {
     throw error(kUnknownError, "PageRank failed to converge.");
   }
@@ -620,10 +635,13 @@ static void katz_sg(b200_handle* h, b200_graph* g, const b200_katz_params_t* p, 
   const unsigned vg = vgrid(n, h->sm_count);
   dbuf<iter_state> d_state(1, s);
   CUDA_TRY(cudaMemsetAsync(d_state.data(), 0, sizeof(iter_state), s));
-  if (!p->has_initial_guess) CUDA_TRY(cudaMemsetAsync(kc, 0, n * sizeof(RT), s));
-  dbuf<RT> tmp(n, s);
+  dbuf<RT> work0(n, s, 8), work1(n, s, 8);  // padded: staged by 16-byte pieces
+  if (p->has_initial_guess)
+    CUDA_TRY(cudaMemcpyAsync(work0.data(), kc, n * sizeof(RT), cudaMemcpyDeviceToDevice, s));
+  else
+    CUDA_TRY(cudaMemsetAsync(work0.data(), 0, n * sizeof(RT), s));
   // buffers alternate; iteration `it` reads buf[it & 1] and writes buf[(it + 1) & 1]
-  RT* buf[2] = {kc, tmp.data()};
+  RT* buf[2] = {work0.data(), work1.data()};
 
   epi_katz<RT> epi{};
   epi.betas = static_cast<const RT*>(p->betas);
@@ -655,8 +673,7 @@ static void katz_sg(b200_handle* h, b200_graph* g, const b200_katz_params_t* p, 
   }
   if (!fixed && !hs.converged) throw error(kUnknownError, "Katz Centrality failed to converge.");
   RT* result = buf[hs.iterations & 1];
-  if (result != kc)
-    CUDA_TRY(cudaMemcpyAsync(kc, result, n * sizeof(RT), cudaMemcpyDeviceToDevice, s));
+  CUDA_TRY(cudaMemcpyAsync(kc, result, n * sizeof(RT), cudaMemcpyDeviceToDevice, s));
   if (p->normalize) {
     RT l2 = static_cast<RT>(std::sqrt(static_cast<RT>(hs.a)));
     B200_EXPECTS(l2 > RT(0), kUnknownError,

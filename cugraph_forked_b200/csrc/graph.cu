@@ -268,6 +268,40 @@ __global__ void row_tiles_kernel(const ET* offsets, int64_t row_lo, int64_t row_
   tiles[k]     = t;
 }
 
+// first row in [row_lo, row_hi) whose degree is < dthr (degrees are non-increasing there)
+template <typename ET>
+__global__ void degree_split_kernel(const ET* offsets, int64_t row_lo, int64_t row_hi, int64_t dthr,
+                                    int64_t* out)
+{
+  int64_t lo = row_lo, hi = row_hi;
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if (static_cast<int64_t>(offsets[mid + 1]) - static_cast<int64_t>(offsets[mid]) >= dthr) lo = mid + 1;
+    else hi = mid;
+  }
+  *out = lo;
+}
+
+// kind-0 tiles of exactly `rows_per_tile` consecutive rows (the very-low-degree tail)
+template <typename ET>
+__global__ void fixed_row_tiles_kernel(const ET* offsets, int64_t row_lo, int64_t row_hi,
+                                       int rows_per_tile, int64_t ntiles, tile_t* tiles)
+{
+  int64_t k = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  if (k >= ntiles) return;
+  int64_t r0 = row_lo + k * rows_per_tile;
+  int64_t r1 = min(row_hi, r0 + rows_per_tile);
+  tile_t t;
+  t.edge_first = static_cast<int64_t>(offsets[r0]);
+  t.num_edges  = static_cast<int32_t>(static_cast<int64_t>(offsets[r1]) - t.edge_first);
+  t.row_first  = static_cast<int32_t>(r0);
+  t.num_rows   = static_cast<int32_t>(r1 - r0);
+  t.aux        = 0;
+  t.kind       = 0;
+  t.pad        = 0;
+  tiles[k]     = t;
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------------
@@ -301,13 +335,28 @@ static void build_schedule_t(b200_handle* h, edge_partition& ep, int T)
     }
   }
   chunk_first[n_long] = static_cast<int64_t>(chunk_tiles.size());
+  // rows [n_long, r_split) have degree >= dthr: windows of T edges hold <= kMaxTileRows rows;
+  // rows [r_split, n_nz) (degree < dthr) are cut into runs of kMaxTileRows rows (< T edges)
+  const int64_t dthr = div_up(T, kMaxTileRows);
+  int64_t r_split    = n_nz;
+  if (n_nz > n_long) {
+    dbuf<int64_t> d_split(1, s);
+    degree_split_kernel<ET><<<1, 1, 0, s>>>(off, n_long, n_nz, dthr, d_split.data());
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(&r_split, d_split.data(), 8, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+  }
+  ET h_split_off = 0;
+  CUDA_TRY(cudaMemcpyAsync(&h_split_off, off + r_split, sizeof(ET), cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaStreamSynchronize(s));
   int64_t edge_lo     = h_off[n_long];
-  int64_t n_row_tiles = (n_nz > n_long) ? div_up(ep.num_edges - edge_lo, T) : 0;
-  if (n_nz > n_long && n_row_tiles == 0) n_row_tiles = 1;  // rows present but no edges
+  int64_t edge_hi     = static_cast<int64_t>(h_split_off);
+  int64_t n_row_tiles = (r_split > n_long) ? std::max<int64_t>(div_up(edge_hi - edge_lo, T), 1) : 0;
+  int64_t n_fix_tiles = div_up(n_nz - r_split, kMaxTileRows);
   ep.num_chunks    = static_cast<int64_t>(chunk_tiles.size());
   ep.num_long_rows = n_long;
-  ep.num_tiles     = ep.num_chunks + n_row_tiles;
-  ep.tiles.alloc(static_cast<size_t>(ep.num_tiles), s);
+  ep.num_tiles     = ep.num_chunks + n_row_tiles + n_fix_tiles;
+  ep.tiles.alloc(static_cast<size_t>(std::max<int64_t>(ep.num_tiles, 1)), s);
   if (!chunk_tiles.empty())
     CUDA_TRY(cudaMemcpyAsync(ep.tiles.data(), chunk_tiles.data(), chunk_tiles.size() * sizeof(tile_t),
                              cudaMemcpyHostToDevice, s));
@@ -316,7 +365,12 @@ static void build_schedule_t(b200_handle* h, edge_partition& ep, int T)
                            chunk_first.size() * sizeof(int64_t), cudaMemcpyHostToDevice, s));
   if (n_row_tiles > 0) {
     row_tiles_kernel<ET><<<grid_for(n_row_tiles), kThreads, 0, s>>>(
-      off, n_long, n_nz, edge_lo, T, n_row_tiles, ep.tiles.data() + ep.num_chunks);
+      off, n_long, r_split, edge_lo, T, n_row_tiles, ep.tiles.data() + ep.num_chunks);
+    CUDA_TRY(cudaGetLastError());
+  }
+  if (n_fix_tiles > 0) {
+    fixed_row_tiles_kernel<ET><<<grid_for(n_fix_tiles), kThreads, 0, s>>>(
+      off, r_split, n_nz, kMaxTileRows, n_fix_tiles, ep.tiles.data() + ep.num_chunks + n_row_tiles);
     CUDA_TRY(cudaGetLastError());
   }
   CUDA_TRY(cudaStreamSynchronize(s));

@@ -12,6 +12,8 @@ namespace b200 {
 constexpr int64_t kLowDegreeThreshold  = 32;
 constexpr int64_t kMidDegreeThreshold  = 1024;
 constexpr double kHypersparseRatio     = 0.5;
+// rows per tile of the pull kernel's schedule (= kRowStageCap in spmv.cuh)
+constexpr int kMaxTileRows             = 1024;
 
 void graph_create_sg(b200_handle* h, const void* src, const void* dst, const void* weights,
                      size_t ne, int vertex_type, int weight_type, const void* vertices,
