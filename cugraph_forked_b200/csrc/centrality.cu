@@ -27,27 +27,41 @@ inline unsigned vgrid(size_t n, int sm_count)
 }
 
 // ---- kernel configurations -----------------------------------------------------------------
-template <int T_, int STAGES_>
+// T = edges per tile, STAGES = depth of the TMA ring, ROWCAP = most rows per tile
+template <int T_, int STAGES_, int ROWCAP_>
 struct pull_cfg {
   static constexpr int T      = T_;
   static constexpr int STAGES = STAGES_;
+  static constexpr int ROWCAP = ROWCAP_;
 };
 template <typename RT, bool WEIGHTED>
 struct default_cfg {
-  using type = pull_cfg<4096, 3>;  // f32 unweighted: 3 x 24.6 KB ring + hub cache
+  using type = pull_cfg<4096, 3, 1024>;  // f32 unweighted (best of the sweep in profiles/)
 };
 template <>
 struct default_cfg<float, true> {
-  using type = pull_cfg<2048, 3>;
+  using type = pull_cfg<2048, 4, 512>;
 };
 template <>
 struct default_cfg<double, false> {
-  using type = pull_cfg<2048, 3>;
+  using type = pull_cfg<2048, 4, 512>;
 };
 template <>
 struct default_cfg<double, true> {
-  using type = pull_cfg<1024, 3>;
+  using type = pull_cfg<1024, 4, 256>;
 };
+// alternatives for tuning sweeps (B200_PULL_CFG=1..), f32 unweighted int32 offsets only
+template <int ID>
+struct alt_cfg {
+  using type = pull_cfg<4096, 3, 1024>;
+};
+template <> struct alt_cfg<1> { using type = pull_cfg<2048, 6, 512>; };
+template <> struct alt_cfg<2> { using type = pull_cfg<4096, 4, 1024>; };
+template <> struct alt_cfg<3> { using type = pull_cfg<2048, 4, 512>; };
+template <> struct alt_cfg<4> { using type = pull_cfg<2048, 8, 512>; };
+template <> struct alt_cfg<5> { using type = pull_cfg<1024, 8, 256>; };
+constexpr int kNumAltCfg = 6;
+
 int env_int(const char* name, int dflt)
 {
   const char* v = std::getenv(name);
@@ -111,6 +125,8 @@ struct pull_launcher {
   int tail_ctas{1};
   int slots{0};
   int T{0};
+  int rowcap{0};
+  int cfg_id{0};
   bool tiled{false};
   int64_t launches{0};
 
@@ -163,13 +179,31 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
     }
   }
   tiled = ep->has_segments;
-  T     = weighted ? default_cfg<RT, true>::type::T : default_cfg<RT, false>::type::T;
+  cfg_id = 0;
+  if (weighted) {
+    T      = default_cfg<RT, true>::type::T;
+    rowcap = default_cfg<RT, true>::type::ROWCAP;
+  } else {
+    T      = default_cfg<RT, false>::type::T;
+    rowcap = default_cfg<RT, false>::type::ROWCAP;
+  }
+  if (sizeof(RT) == 4 && !weighted && !ep->offsets64) {
+    cfg_id = std::max(0, std::min(kNumAltCfg - 1, env_int("B200_PULL_CFG", 0)));
+    const int ts[kNumAltCfg] = {alt_cfg<0>::type::T, alt_cfg<1>::type::T, alt_cfg<2>::type::T,
+                                alt_cfg<3>::type::T, alt_cfg<4>::type::T, alt_cfg<5>::type::T};
+    const int rs[kNumAltCfg] = {alt_cfg<0>::type::ROWCAP, alt_cfg<1>::type::ROWCAP,
+                                alt_cfg<2>::type::ROWCAP, alt_cfg<3>::type::ROWCAP,
+                                alt_cfg<4>::type::ROWCAP, alt_cfg<5>::type::ROWCAP};
+    T      = ts[cfg_id];
+    rowcap = rs[cfg_id];
+  }
   if (tiled) {
-    build_schedule(h, *ep, T);
+    build_schedule(h, *ep, T, rowcap);
     main_ctas = h->sm_count;  // one persistent warp-specialised CTA per SM
     if (ep->num_tiles < main_ctas) main_ctas = static_cast<int>(std::max<int64_t>(ep->num_tiles, 1));
-    int64_t want_tail = div_up(std::max<int64_t>(ep->num_long_rows, 1), 8);
-    tail_ctas         = static_cast<int>(std::min<int64_t>(want_tail, 64));
+    // tail kernel: 8 lanes per long row, 32 rows per 256-thread block
+    int64_t want_tail = div_up(std::max<int64_t>(ep->num_long_rows, 1), 32);
+    tail_ctas         = static_cast<int>(std::min<int64_t>(want_tail, 8 * h->sm_count));
   } else {
     main_ctas = h->sm_count * 8;
     tail_ctas = 1;
@@ -218,12 +252,12 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
   P.slots          = slots;
   P.state          = state;
   const int hub_cap = env_int("B200_HUB_ENTRIES", 1 << 30);
-  auto go = [&](auto et, auto wtag) {
+  auto launch = [&](auto et, auto wtag, auto cfgtag) {
     using ET         = decltype(et);
     constexpr bool W = decltype(wtag)::value;
-    using CFG        = typename default_cfg<RT, W>::type;
-    using SM         = pull_smem<ET, RT, W, CFG::T, CFG::STAGES, EPI::kStage>;
-    auto kern        = pull_tiles_kernel<ET, RT, W, EPI, CFG::T, CFG::STAGES>;
+    using CFG        = typename decltype(cfgtag)::type;
+    using SM         = pull_smem<ET, RT, W, CFG::T, CFG::STAGES, CFG::ROWCAP, EPI::kStage>;
+    auto kern        = pull_tiles_kernel<ET, RT, W, EPI, CFG::T, CFG::STAGES, CFG::ROWCAP>;
     // the hub cache takes what is left of the shared-memory budget; the budget leaves L1 enough
     // lines to track the outstanding gathers (profiles/microbench_gather.md)
     const int64_t budget = static_cast<int64_t>(env_int("B200_SMEM_BUDGET_KB", 160)) * 1024;
@@ -238,6 +272,21 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
     }
     P.hub_entries = hub;
     kern<<<main_ctas, kPullThreads, SM::total(hub), s>>>(P, epi);
+  };
+  auto go = [&](auto et, auto wtag) {
+    using ET         = decltype(et);
+    constexpr bool W = decltype(wtag)::value;
+    if constexpr (sizeof(RT) == 4 && !W && std::is_same<ET, int32_t>::value) {
+      switch (cfg_id) {
+        case 1: launch(et, wtag, alt_cfg<1>{}); return;
+        case 2: launch(et, wtag, alt_cfg<2>{}); return;
+        case 3: launch(et, wtag, alt_cfg<3>{}); return;
+        case 4: launch(et, wtag, alt_cfg<4>{}); return;
+        case 5: launch(et, wtag, alt_cfg<5>{}); return;
+        default: break;
+      }
+    }
+    launch(et, wtag, default_cfg<RT, W>{});
   };
   if (ep->offsets64) {
     if (weighted) go(int64_t{}, std::true_type{}); else go(int64_t{}, std::false_type{});

@@ -168,6 +168,7 @@ struct edge_partition {
   bool has_segments{false};
   // schedule (one per tile capacity; built lazily by spmv.cu)
   int32_t sched_tile_edges{0};
+  int32_t sched_row_cap{0};
   dbuf<tile_t> tiles;
   int64_t num_tiles{0};
   int64_t num_chunks{0};          // kind-1 tiles

@@ -308,7 +308,7 @@ __global__ void fixed_row_tiles_kernel(const ET* offsets, int64_t row_lo, int64_
 // schedule
 // ------------------------------------------------------------------------------------------
 template <typename ET>
-static void build_schedule_t(b200_handle* h, edge_partition& ep, int T)
+static void build_schedule_t(b200_handle* h, edge_partition& ep, int T, int rowcap)
 {
   cudaStream_t s = h->stream;
   const ET* off  = reinterpret_cast<const ET*>(ep.offsets.data());
@@ -335,9 +335,9 @@ static void build_schedule_t(b200_handle* h, edge_partition& ep, int T)
     }
   }
   chunk_first[n_long] = static_cast<int64_t>(chunk_tiles.size());
-  // rows [n_long, r_split) have degree >= dthr: windows of T edges hold <= kMaxTileRows rows;
-  // rows [r_split, n_nz) (degree < dthr) are cut into runs of kMaxTileRows rows (< T edges)
-  const int64_t dthr = div_up(T, kMaxTileRows);
+  // rows [n_long, r_split) have degree >= dthr: windows of T edges hold <= rowcap rows;
+  // rows [r_split, n_nz) (degree < dthr) are cut into runs of rowcap rows (< T edges)
+  const int64_t dthr = div_up(T, rowcap);
   int64_t r_split    = n_nz;
   if (n_nz > n_long) {
     dbuf<int64_t> d_split(1, s);
@@ -352,7 +352,7 @@ static void build_schedule_t(b200_handle* h, edge_partition& ep, int T)
   int64_t edge_lo     = h_off[n_long];
   int64_t edge_hi     = static_cast<int64_t>(h_split_off);
   int64_t n_row_tiles = (r_split > n_long) ? std::max<int64_t>(div_up(edge_hi - edge_lo, T), 1) : 0;
-  int64_t n_fix_tiles = div_up(n_nz - r_split, kMaxTileRows);
+  int64_t n_fix_tiles = div_up(n_nz - r_split, rowcap);
   ep.num_chunks    = static_cast<int64_t>(chunk_tiles.size());
   ep.num_long_rows = n_long;
   ep.num_tiles     = ep.num_chunks + n_row_tiles + n_fix_tiles;
@@ -370,18 +370,19 @@ static void build_schedule_t(b200_handle* h, edge_partition& ep, int T)
   }
   if (n_fix_tiles > 0) {
     fixed_row_tiles_kernel<ET><<<grid_for(n_fix_tiles), kThreads, 0, s>>>(
-      off, r_split, n_nz, kMaxTileRows, n_fix_tiles, ep.tiles.data() + ep.num_chunks + n_row_tiles);
+      off, r_split, n_nz, rowcap, n_fix_tiles, ep.tiles.data() + ep.num_chunks + n_row_tiles);
     CUDA_TRY(cudaGetLastError());
   }
   CUDA_TRY(cudaStreamSynchronize(s));
   ep.sched_tile_edges = T;
+  ep.sched_row_cap    = rowcap;
 }
 
-void build_schedule(b200_handle* h, edge_partition& ep, int T)
+void build_schedule(b200_handle* h, edge_partition& ep, int T, int rowcap)
 {
-  if (ep.sched_tile_edges == T) return;
-  if (ep.offsets64) build_schedule_t<int64_t>(h, ep, T);
-  else build_schedule_t<int32_t>(h, ep, T);
+  if (ep.sched_tile_edges == T && ep.sched_row_cap == rowcap) return;
+  if (ep.offsets64) build_schedule_t<int64_t>(h, ep, T, rowcap);
+  else build_schedule_t<int32_t>(h, ep, T, rowcap);
 }
 
 // ------------------------------------------------------------------------------------------

@@ -12,15 +12,13 @@ namespace b200 {
 constexpr int64_t kLowDegreeThreshold  = 32;
 constexpr int64_t kMidDegreeThreshold  = 1024;
 constexpr double kHypersparseRatio     = 0.5;
-// rows per tile of the pull kernel's schedule (= kRowStageCap in spmv.cuh)
-constexpr int kMaxTileRows             = 1024;
 
 void graph_create_sg(b200_handle* h, const void* src, const void* dst, const void* weights,
                      size_t ne, int vertex_type, int weight_type, const void* vertices,
                      size_t n_given, bool store_transposed, bool renumber, b200_graph* g);
 void graph_out_weight_sums(b200_handle* h, b200_graph* g);
 void graph_in_degrees(b200_handle* h, const b200_graph* g, void* out);
-// (re)build the tile schedule of one edge partition for tiles of T edges
-void build_schedule(b200_handle* h, edge_partition& ep, int T);
+// (re)build the tile schedule of one edge partition: tiles of <= T edges and <= rowcap rows
+void build_schedule(b200_handle* h, edge_partition& ep, int T, int rowcap);
 
 }  // namespace b200

@@ -55,7 +55,6 @@ struct pull_params {
 };
 
 constexpr int kLongRowDegree = 1024;  // = mid_degree_threshold, graph_view.hpp:255-263
-constexpr int kRowStageCap   = 1024;  // the schedule never puts more rows into one tile
 
 constexpr int kGatherWarps  = 16;
 constexpr int kReduceWarps  = 15;
@@ -64,14 +63,15 @@ constexpr int kGatherThreads = kGatherWarps * 32;
 constexpr int kReduceThreads = kReduceWarps * 32;
 
 // shared-memory geometry of one CTA (dynamic part): [hub | ring stages | product ring]
-template <typename ET, typename RT, bool WEIGHTED, int T, int STAGES, int NSTAGED>
+// ROWCAP = most rows the schedule puts into one tile (their offsets and epilogue inputs are staged)
+template <typename ET, typename RT, bool WEIGHTED, int T, int STAGES, int ROWCAP, int NSTAGED>
 struct pull_smem {
   // staged element capacity: T edges + one row overhang (< 1024) + alignment slack
   static constexpr int cap       = T + kLongRowDegree + 8;
   static constexpr size_t idx_b  = size_t(cap) * 4;
   static constexpr size_t w_b    = WEIGHTED ? size_t(cap) * sizeof(RT) : 0;
-  static constexpr size_t off_b  = size_t(kRowStageCap + 8) * sizeof(ET);
-  static constexpr size_t in_b   = size_t(kRowStageCap + 8) * sizeof(RT);  // one staged epilogue input
+  static constexpr size_t off_b  = size_t(ROWCAP + 8) * sizeof(ET);
+  static constexpr size_t in_b   = size_t(ROWCAP + 8) * sizeof(RT);  // one staged epilogue input
   static constexpr size_t stage  = ((idx_b + w_b + off_b + NSTAGED * in_b) + 127) & ~size_t(127);
   // 4-byte results overwrite the staged indices in place; 8-byte results get their own ring
   static constexpr bool inplace  = sizeof(RT) == 4;
@@ -85,11 +85,11 @@ struct pull_smem {
 // ------------------------------------------------------------------------------------------
 // the kernel
 // ------------------------------------------------------------------------------------------
-template <typename ET, typename RT, bool WEIGHTED, typename EPI, int T, int STAGES>
+template <typename ET, typename RT, bool WEIGHTED, typename EPI, int T, int STAGES, int ROWCAP>
 __global__ void __launch_bounds__(kPullThreads, 1)
   pull_tiles_kernel(const __grid_constant__ pull_params P, EPI epi)
 {
-  using S = pull_smem<ET, RT, WEIGHTED, T, STAGES, EPI::kStage>;
+  using S = pull_smem<ET, RT, WEIGHTED, T, STAGES, ROWCAP, EPI::kStage>;
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ uint64_t full_bar[STAGES];   // TMA landed            (1 arrival + tx bytes)
   __shared__ uint64_t ready_bar[STAGES];  // products written      (kGatherWarps arrivals)
@@ -371,15 +371,26 @@ __global__ void __launch_bounds__(THREADS) pull_tail_kernel(const __grid_constan
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   epi.setup(P.state);
   acc2 acc;
-  const int64_t warps_total = static_cast<int64_t>(gridDim.x) * (THREADS / 32);
-  for (int64_t r = static_cast<int64_t>(blockIdx.x) * (THREADS / 32) + warp; r < P.num_long_rows;
-       r += warps_total) {
-    const int64_t c0 = P.long_row_chunk_first[r], c1 = P.long_row_chunk_first[r + 1];
-    double s = 0.0;
-    for (int64_t c = c0 + lane; c < c1; c += 32) s += P.chunk_partials[c];
-    s = warp_sum(s);
-    if (lane == 0) epi(r, static_cast<RT>(s), acc);
+  // 8 lanes per long row (most long rows have a handful of chunks); fixed order => deterministic
+  constexpr int G           = 8;
+  const int64_t groups_total = static_cast<int64_t>(gridDim.x) * (THREADS / G);
+  const int l               = tid % G;
+  const int64_t rounds      = (P.num_long_rows + groups_total - 1) / groups_total;
+  for (int64_t k = 0; k < rounds; ++k) {
+    const int64_t r = k * groups_total + static_cast<int64_t>(blockIdx.x) * (THREADS / G) + tid / G;
+    const bool act  = r < P.num_long_rows;
+    double s        = 0.0;
+    typename EPI::pre_t pre{};
+    if (act) {
+      const int64_t c0 = P.long_row_chunk_first[r], c1 = P.long_row_chunk_first[r + 1];
+      if (l == 0) pre = epi.prefetch(r);
+      for (int64_t c = c0 + l; c < c1; c += G) s += P.chunk_partials[c];
+    }
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o, G);
+    if (act && l == 0) epi.finish(r, static_cast<RT>(s), pre, acc);
   }
+  (void)lane; (void)warp;
   if (!P.cta_partials) return;
   double a = block_sum(acc.a, red_scratch);
   double b = block_sum(acc.b, red_scratch);
