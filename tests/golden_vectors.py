@@ -1,0 +1,39 @@
+"""Golden vectors held by the reference's own C-API tests (compared there with relative 1e-3,
+cpp/tests/c_api/test_utils.cpp:21-27)."""
+import numpy as np
+
+# cpp/tests/c_api/pagerank_test.c:211-249 (and katz_test.c:103-129 on the same graph)
+G6_SRC = np.array([0, 1, 1, 2, 2, 2, 3, 4], np.int32)
+G6_DST = np.array([1, 3, 4, 0, 1, 3, 5, 5], np.int32)
+G6_WGT = np.array([0.1, 2.1, 1.1, 5.1, 3.1, 4.1, 7.2, 3.2], np.float32)
+G6_PAGERANK = dict(alpha=0.95, epsilon=1e-4, max_iterations=20,
+                   result=np.array([0.0915528, 0.168382, 0.0656831, 0.191468, 0.120677, 0.362237]))
+G6_KATZ = dict(alpha=0.01, beta=1.0, epsilon=1e-6, max_iterations=1000,
+               result=np.array([0.410614, 0.403211, 0.390689, 0.415175, 0.395125, 0.433226]))
+
+# cpp/tests/c_api/pagerank_test.c:251-287; also the doctest of pylibcugraph/pagerank.pyx:135-146
+P4_SRC = np.array([0, 1, 2], np.int32)
+P4_DST = np.array([1, 2, 3], np.int32)
+P4_WGT = np.array([1.0, 1.0, 1.0], np.float32)
+P4_PAGERANK = dict(alpha=0.85, epsilon=1e-6, max_iterations=500,
+                   result=np.array([0.11615584790706635, 0.21488840878009796,
+                                    0.29881080985069275, 0.37014490365982056]))
+# cpp/tests/c_api/pagerank_test.c:289-318
+P4_PERSONALIZED = dict(alpha=0.85, epsilon=1e-6, max_iterations=500,
+                       vertices=np.array([0, 1, 2, 3], np.int32),
+                       values=np.array([0.1, 0.2, 0.3, 0.4], np.float32),
+                       result=np.array([0.0559233, 0.159381, 0.303244, 0.481451]))
+
+# cpp/tests/c_api/eigenvector_centrality_test.c:93-110
+E6_SRC = np.array([0, 1, 1, 2, 2, 2, 3, 4, 1, 3, 4, 0, 1, 3, 5, 5], np.int32)
+E6_DST = np.array([1, 3, 4, 0, 1, 3, 5, 5, 0, 1, 1, 2, 2, 2, 3, 4], np.int32)
+E6_WGT = np.array([0.1, 2.1, 1.1, 5.1, 3.1, 4.1, 7.2, 3.2] * 2, np.float32)
+E6_EIGENVECTOR = dict(epsilon=1e-6, max_iterations=200,
+                      result=np.array([0.236325, 0.292055, 0.458457, 0.60533, 0.190498, 0.495942]))
+
+
+def nearly_equal(a, b, eps=1e-3):
+    """cpp/tests/c_api/test_utils.cpp:21-27"""
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    return np.all(np.abs(a - b) <= eps * np.maximum(np.abs(a), np.abs(b)))
