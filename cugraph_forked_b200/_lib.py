@@ -57,6 +57,8 @@ class CentralityStats(ctypes.Structure):
         ("last_diff", ctypes.c_double),
         ("elapsed_ms", ctypes.c_double),
         ("gpu_launches", ctypes.c_int64),
+        ("spmv_ms", ctypes.c_double),
+        ("spmv_launches", ctypes.c_int64),
     ]
 
 

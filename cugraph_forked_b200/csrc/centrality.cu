@@ -499,6 +499,46 @@ struct loop_timer {
   }
 };
 
+// CUDA events around every pull-kernel launch (first kMax iterations): the roofline figure of
+// bench.py is algorithmic bytes / this duration
+struct launch_timer {
+  static constexpr int kMax = 256;
+  std::vector<cudaEvent_t> ev;
+  cudaStream_t s;
+  int n{0};
+  explicit launch_timer(cudaStream_t s_) : s(s_) {}
+  ~launch_timer() { for (auto e : ev) cudaEventDestroy(e); }
+  void before()
+  {
+    if (n >= kMax) return;
+    cudaEvent_t a, b;
+    cudaEventCreate(&a);
+    cudaEventCreate(&b);
+    ev.push_back(a);
+    ev.push_back(b);
+    cudaEventRecord(a, s);
+  }
+  void after()
+  {
+    if (n >= kMax) return;
+    cudaEventRecord(ev[2 * n + 1], s);
+    ++n;
+  }
+  // call after the stream has been synchronised
+  void collect(b200_centrality_stats_t* st)
+  {
+    if (!st) return;
+    double tot = 0.0;
+    for (int i = 0; i < n; ++i) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, ev[2 * i], ev[2 * i + 1]);
+      tot += ms;
+    }
+    st->spmv_ms       = tot;
+    st->spmv_launches = n;
+  }
+};
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------------
@@ -613,12 +653,15 @@ static void pagerank_sg(b200_handle* h, b200_graph* g, const b200_pagerank_param
 
   const int check_every = std::max(1, env_int("B200_CHECK_EVERY", 8));
   loop_timer timer(s);
+  launch_timer ktimer(s);
   timer.start();
   iter_state hs{};
   int64_t it = 0;
   for (; it < cap; ++it) {
     epi.x_next = x[(it + 1) & 1];
+    ktimer.before();
     L.spmv(x[it & 1], epi, d_state.data(), true);
+    ktimer.after();
     L.tail(epi, d_state.data(), static_cast<double>(epsilon), it + 1, !fixed, true);
     if (!fixed && ((it + 1) % check_every == 0)) {
       read_state(h, d_state.data(), &hs);
@@ -633,6 +676,7 @@ static void pagerank_sg(b200_handle* h, b200_graph* g, const b200_pagerank_param
     stats->last_diff    = hs.b;
     stats->elapsed_ms   = ms;
     stats->gpu_launches = L.launches;
+    ktimer.collect(stats);
   }
   CUDA_TRY(cudaMemcpyAsync(pr_user, pr, n * sizeof(RT), cudaMemcpyDeviceToDevice, s));
   CUDA_TRY(cudaStreamSynchronize(s));

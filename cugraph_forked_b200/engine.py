@@ -39,6 +39,8 @@ class Stats:
     last_diff: float
     elapsed_ms: float
     gpu_launches: int
+    spmv_ms: float = 0.0
+    spmv_launches: int = 0
 
 
 class Handle:
@@ -199,7 +201,7 @@ class Graph:
 
 def _stats(s: _lib.CentralityStats) -> Stats:
     return Stats(int(s.iterations), bool(s.converged), float(s.last_diff), float(s.elapsed_ms),
-                 int(s.gpu_launches))
+                 int(s.gpu_launches), float(s.spmv_ms), int(s.spmv_launches))
 
 
 def spmv_pull(graph: Graph, x: torch.Tensor, scale: float = 1.0, init: float = 0.0) -> torch.Tensor:

@@ -131,6 +131,9 @@ typedef struct b200_centrality_stats {
   double last_diff;     /* L1 difference of the last executed iteration                        */
   double elapsed_ms;    /* device time of the iteration loop (CUDA events on the handle stream) */
   int64_t gpu_launches; /* kernels launched by the loop                                        */
+  double spmv_ms;       /* summed device time of the pull-kernel launches alone (CUDA events     */
+                        /* around every launch of the first 256 iterations)                     */
+  int64_t spmv_launches; /* launches covered by spmv_ms                                        */
 } b200_centrality_stats_t;
 
 typedef struct b200_pagerank_params {
