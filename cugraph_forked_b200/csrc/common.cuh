@@ -197,6 +197,10 @@ struct b200_graph {
   // cached out-weight sums (double precision master copy, local vertices)
   b200::dbuf<double> out_weight_sums;
   bool have_out_weight_sums{false};
+  // sorted (external id, internal id) pairs of the local vertices, built on first use
+  b200::dbuf<uint64_t> ext_sorted;
+  b200::dbuf<uint32_t> ext_internal;
+  bool have_ext_map{false};
   // the COO in external ids is not kept; a graph stored the other way round is rebuilt from a
   // decompressed edge list when a pull algorithm needs it (c_api/graph.hpp:44-79 does the same)
 };

@@ -780,4 +780,141 @@ void graph_in_degrees(b200_handle* h, const b200_graph* g, void* out)
   CUDA_TRY(cudaStreamSynchronize(h->stream));
 }
 
+
+// ------------------------------------------------------------------------------------------
+// external id -> internal id (renumber_local_ext_vertices / collect_local_vertex_values_from_
+// ext_vertex_value_pairs of the reference's C API glue, c_api/pagerank.cpp:125-210)
+// ------------------------------------------------------------------------------------------
+namespace {
+template <typename VT>
+__global__ void map_keys_kernel(const VT* labels, size_t n, uint64_t* keys, uint32_t* vals)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    keys[i] = static_cast<uint64_t>(labels[i]);
+    vals[i] = static_cast<uint32_t>(i);
+  }
+}
+template <typename VT>
+__global__ void lookup_kernel(const uint64_t* sorted_ext, const uint32_t* sorted_int, size_t n_map,
+                              const VT* query, size_t n, int32_t* out)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    uint64_t q = static_cast<uint64_t>(query[i]);
+    size_t lo = 0, hi = n_map;
+    while (lo < hi) {
+      size_t mid = (lo + hi) >> 1;
+      if (sorted_ext[mid] < q) lo = mid + 1;
+      else hi = mid;
+    }
+    out[i] = (lo < n_map && sorted_ext[lo] == q && query[i] >= 0) ? static_cast<int32_t>(sorted_int[lo])
+                                                                   : -1;
+  }
+}
+template <typename VT, typename WT>
+__global__ void decompress_kernel(const void* offsets_v, int offsets64, const int32_t* indices,
+                                  const WT* w_in, const VT* labels, int64_t num_rows,
+                                  int64_t minor_first, int majors_are_dst, VT* src, VT* dst,
+                                  WT* w_out)
+{
+  // one warp per row
+  const int lane     = threadIdx.x & 31;
+  const int64_t warp = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5;
+  const int64_t nw   = (int64_t(gridDim.x) * blockDim.x) >> 5;
+  for (int64_t r = warp; r < num_rows; r += nw) {
+    int64_t b, e;
+    if (offsets64) {
+      b = static_cast<const int64_t*>(offsets_v)[r];
+      e = static_cast<const int64_t*>(offsets_v)[r + 1];
+    } else {
+      b = static_cast<const int32_t*>(offsets_v)[r];
+      e = static_cast<const int32_t*>(offsets_v)[r + 1];
+    }
+    VT major = labels[r];
+    for (int64_t i = b + lane; i < e; i += 32) {
+      VT minor = labels[minor_first + indices[i]];
+      src[i]   = majors_are_dst ? minor : major;
+      dst[i]   = majors_are_dst ? major : minor;
+      if (w_in) w_out[i] = w_in[i];
+    }
+  }
+}
+}  // namespace
+
+void graph_ext_to_internal(b200_handle* h, b200_graph* g, const void* ext_ids, size_t n,
+                           int32_t* out)
+{
+  cudaStream_t s = h->stream;
+  size_t nloc    = static_cast<size_t>(g->local_last - g->local_first);
+  if (!g->have_ext_map) {
+    dbuf<uint64_t> k0(nloc, s), k1(nloc, s);
+    dbuf<uint32_t> v0(nloc, s), v1(nloc, s);
+    if (nloc) {
+      if (g->vertex_type == B200_INT32)
+        map_keys_kernel<int32_t><<<grid_for(nloc, 4), kThreads, 0, s>>>(
+          reinterpret_cast<const int32_t*>(g->renumber_map.data()), nloc, k0.data(), v0.data());
+      else
+        map_keys_kernel<int64_t><<<grid_for(nloc, 4), kThreads, 0, s>>>(
+          reinterpret_cast<const int64_t*>(g->renumber_map.data()), nloc, k0.data(), v0.data());
+      CUDA_TRY(cudaGetLastError());
+    }
+    int where = radix_sort<uint64_t>(k0.data(), k1.data(), v0.data(), v1.data(), nloc, {{0, 63}}, s);
+    g->ext_sorted   = where ? std::move(k1) : std::move(k0);
+    g->ext_internal = where ? std::move(v1) : std::move(v0);
+    g->have_ext_map = true;
+  }
+  if (n == 0) return;
+  if (g->vertex_type == B200_INT32)
+    lookup_kernel<int32_t><<<grid_for(n, 2), kThreads, 0, s>>>(
+      g->ext_sorted.data(), g->ext_internal.data(), nloc, static_cast<const int32_t*>(ext_ids), n, out);
+  else
+    lookup_kernel<int64_t><<<grid_for(n, 2), kThreads, 0, s>>>(
+      g->ext_sorted.data(), g->ext_internal.data(), nloc, static_cast<const int64_t*>(ext_ids), n, out);
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaStreamSynchronize(s));
+}
+
+// Rebuilds a single-GPU graph with the other storage orientation, in place (what
+// cugraph::c_api::transpose_storage does before a pull algorithm, c_api/graph.hpp:44-79):
+// decompress to an external-id COO, then run the normal build with the full vertex list.
+void graph_transpose_storage(b200_handle* h, b200_graph* g)
+{
+  B200_EXPECTS(!g->multi_gpu, kNotImplemented, "transpose_storage of a multi-GPU graph");
+  cudaStream_t s     = h->stream;
+  edge_partition& ep = g->parts[0];
+  size_t ne          = static_cast<size_t>(ep.num_edges);
+  size_t nv          = static_cast<size_t>(g->num_vertices);
+  int vs             = dtype_size(g->vertex_type);
+  int ws             = dtype_size(g->weight_type);
+  dbuf<char> src(ne * vs, s), dst(ne * vs, s), w(g->weighted ? ne * ws : 0, s);
+  if (ne) {
+    unsigned grid = grid_for(nv * 32, 1);
+    if (grid > 65535u * 8) grid = 65535u * 8;
+    auto run = [&](auto vt, auto wt) {
+      using VT = decltype(vt);
+      using WT = decltype(wt);
+      decompress_kernel<VT, WT><<<grid, kThreads, 0, s>>>(
+        ep.offsets.data(), ep.offsets64 ? 1 : 0, ep.indices.data(),
+        g->weighted ? reinterpret_cast<const WT*>(ep.weights.data()) : nullptr,
+        reinterpret_cast<const VT*>(g->renumber_map.data()), ep.num_rows, ep.minor_first,
+        g->store_transposed ? 1 : 0, reinterpret_cast<VT*>(src.data()),
+        reinterpret_cast<VT*>(dst.data()), reinterpret_cast<WT*>(w.data()));
+    };
+    if (g->vertex_type == B200_INT32) {
+      if (g->weight_type == B200_FLOAT32) run(int32_t{}, float{}); else run(int32_t{}, double{});
+    } else {
+      if (g->weight_type == B200_FLOAT32) run(int64_t{}, float{}); else run(int64_t{}, double{});
+    }
+    CUDA_TRY(cudaGetLastError());
+  }
+  CUDA_TRY(cudaStreamSynchronize(s));
+  b200_graph fresh;
+  // the vertex list keeps isolated vertices; ids stay as they are when the graph was not renumbered
+  graph_create_sg(h, src.data(), dst.data(), g->weighted ? w.data() : nullptr, ne, g->vertex_type,
+                  g->weight_type, g->renumber_map.data(), nv, !g->store_transposed, g->renumbered,
+                  &fresh);
+  *g = std::move(fresh);
+}
+
 }  // namespace b200

@@ -18,6 +18,10 @@ void graph_create_sg(b200_handle* h, const void* src, const void* dst, const voi
                      size_t n_given, bool store_transposed, bool renumber, b200_graph* g);
 void graph_out_weight_sums(b200_handle* h, b200_graph* g);
 void graph_in_degrees(b200_handle* h, const b200_graph* g, void* out);
+// out[i] = internal (local) id of external id ext_ids[i], or -1
+void graph_ext_to_internal(b200_handle* h, b200_graph* g, const void* ext_ids, size_t n,
+                           int32_t* out);
+void graph_transpose_storage(b200_handle* h, b200_graph* g);
 // (re)build the tile schedule of one edge partition: tiles of <= T edges and <= rowcap rows
 void build_schedule(b200_handle* h, edge_partition& ep, int T, int rowcap);
 
