@@ -47,6 +47,10 @@ class GraphView(ctypes.Structure):
         ("col_comm_size", ctypes.c_int32),
         ("local_vertex_first", ctypes.c_int64),
         ("local_vertex_last", ctypes.c_int64),
+        ("major_first", ctypes.c_int64),
+        ("major_last", ctypes.c_int64),
+        ("minor_first", ctypes.c_int64),
+        ("minor_last", ctypes.c_int64),
     ]
 
 
@@ -116,6 +120,7 @@ SIGNATURES = {
     "b200_graph_create_mg": (_i, [_vp, _vp, _vp, _vp, _sz, _i, _i, _vp, _sz, _i, _pp]),
     "b200_graph_view": (_i, [_vp, ctypes.POINTER(GraphView)]),
     "b200_graph_partition_view": (_i, [_vp, _i, ctypes.POINTER(GraphView)]),
+    "b200_graph_vertex_partition_offsets": (_i, [_vp, ctypes.POINTER(ctypes.c_int64)]),
     "b200_graph_free": (None, [_vp]),
     "b200_graph_out_weight_sums": (_i, [_vp, _vp, _i, _vp]),
     "b200_graph_in_degrees": (_i, [_vp, _vp, _vp]),

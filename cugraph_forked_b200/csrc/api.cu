@@ -121,6 +121,7 @@ int b200_handle_create_mg(void* stream, const void* nccl_unique_id, int rank, in
       NCCL_TRY(ncclCommSplit(h->world, col_color, rank, &h->col, nullptr));
       h->row_rank = rank % row_comm_size;
       h->col_rank = rank / row_comm_size;
+      CUDA_TRY(cudaStreamCreateWithFlags(&h->comm_stream, cudaStreamNonBlocking));
     } catch (...) {
       delete h;
       throw;
@@ -138,6 +139,7 @@ void b200_handle_free(b200_handle_t* h)
   if (h->row) ncclCommDestroy(h->row);
   if (h->col) ncclCommDestroy(h->col);
   if (h->world) ncclCommDestroy(h->world);
+  if (h->comm_stream) cudaStreamDestroy(h->comm_stream);
   if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
   delete h;
 }
@@ -209,6 +211,15 @@ static void fill_view(const b200_graph* g, int part, b200_graph_view_t* v)
   v->renumber_map = g->renumber_map.data();
   v->local_vertex_first = g->local_first;
   v->local_vertex_last  = g->local_last;
+  v->major_first        = ep.major_first;
+  v->major_last         = ep.major_first + ep.num_rows;
+  v->minor_first        = ep.minor_first;
+  v->minor_last         = ep.minor_first + ep.num_minors;
+  if (g->multi_gpu && part < static_cast<int>(g->partition_segment_offsets.size())) {
+    auto const& seg = g->partition_segment_offsets[part];
+    v->num_segments = static_cast<int32_t>(seg.size()) - 1;
+    for (size_t i = 0; i < 8; ++i) v->segment_offsets[i] = i < seg.size() ? seg[i] : 0;
+  }
 }
 
 int b200_graph_view(const b200_graph_t* g, b200_graph_view_t* out)
@@ -216,6 +227,26 @@ int b200_graph_view(const b200_graph_t* g, b200_graph_view_t* out)
   return guarded([&] {
     B200_EXPECTS(g && out, kInvalidInput, "NULL argument");
     fill_view(g, 0, out);
+    if (g->multi_gpu) {
+      // the whole-graph view of an MG graph: this rank's vertex partition and its segments
+      out->num_edges    = g->num_edges;
+      out->num_segments = g->num_segments;
+      for (int i = 0; i < 8; ++i) out->segment_offsets[i] = g->segment_offsets[i];
+    }
+  });
+}
+
+int b200_graph_vertex_partition_offsets(const b200_graph_t* g, int64_t* out)
+{
+  return guarded([&] {
+    B200_EXPECTS(g && out, kInvalidInput, "NULL argument");
+    if (g->multi_gpu) {
+      for (size_t i = 0; i < g->vertex_partition_offsets.size(); ++i)
+        out[i] = g->vertex_partition_offsets[i];
+    } else {
+      out[0] = 0;
+      out[1] = g->num_vertices;
+    }
   });
 }
 

@@ -245,7 +245,7 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
   P.indices        = ep->indices.data();
   P.weights        = weights;
   P.x              = x;
-  P.zero_first     = ep->seg[3];
+  P.zero_first     = ep->zero_first;
   P.num_rows       = ep->num_rows;
   P.chunk_partials = chunk_partials.data();
   P.cta_partials   = parts;
@@ -303,6 +303,7 @@ void pull_launcher<RT>::tail(EPI const& epi, iter_state* state, double epsilon, 
                              bool check, bool finalize)
 {
   tail_params P{};
+  P.long_row_ids         = (tiled && ep->generic_schedule) ? ep->long_row_ids.data() : nullptr;
   P.long_row_chunk_first = tiled ? ep->long_row_chunk_first.data() : nullptr;
   P.chunk_partials       = chunk_partials.data();
   P.num_long_rows        = tiled ? ep->num_long_rows : 0;
@@ -869,10 +870,59 @@ void eigenvector_centrality(b200_handle* h, b200_graph* g, const b200_eigenvecto
                "Eigenvector centrality needs a graph stored transposed (pull layout).");
   B200_EXPECTS(p->epsilon >= 0.0, kInvalidInput,
                "Invalid input argument: epsilon should be non-negative.");
-  B200_EXPECTS(!g->multi_gpu, kNotImplemented, "multi-GPU eigenvector centrality");
+  if (g->multi_gpu) {
+    eigenvector_mg(h, g, p, out, stats);
+    return;
+  }
   if (p->value_type == B200_FLOAT32) eigen_sg<float>(h, g, p, static_cast<float*>(out), stats);
   else eigen_sg<double>(h, g, p, static_cast<double*>(out), stats);
 }
+
+// ------------------------------------------------------------------------------------------
+// one edge partition of a multi-GPU graph: y = A_i^T x with the raw epilogue (mg.cu sums the
+// partitions' results over col_comm and runs the driver's vertex pass afterwards)
+// ------------------------------------------------------------------------------------------
+struct partition_spmv {
+  int value_type{B200_FLOAT32};
+  pull_launcher<float> lf;
+  pull_launcher<double> ld;
+};
+
+partition_spmv* partition_spmv_create(b200_handle* h, b200_graph* g, int part, int value_type)
+{
+  auto* p       = new partition_spmv();
+  p->value_type = value_type;
+  try {
+    if (value_type == B200_FLOAT32) p->lf.init(h, g, &g->parts[part]);
+    else p->ld.init(h, g, &g->parts[part]);
+  } catch (...) {
+    delete p;
+    throw;
+  }
+  return p;
+}
+
+void partition_spmv_run(partition_spmv* p, const void* x, void* y, const iter_state* state)
+{
+  if (p->value_type == B200_FLOAT32) {
+    if (p->lf.ep->num_rows == 0) return;
+    epi_raw<float> epi{static_cast<float*>(y), 1.0f, 0.0f};
+    p->lf.spmv(static_cast<const float*>(x), epi, state, false);
+    p->lf.tail(epi, const_cast<iter_state*>(state), 0.0, 0, false, false);
+  } else {
+    if (p->ld.ep->num_rows == 0) return;
+    epi_raw<double> epi{static_cast<double*>(y), 1.0, 0.0};
+    p->ld.spmv(static_cast<const double*>(x), epi, state, false);
+    p->ld.tail(epi, const_cast<iter_state*>(state), 0.0, 0, false, false);
+  }
+}
+
+int64_t partition_spmv_launches(const partition_spmv* p)
+{
+  return p->value_type == B200_FLOAT32 ? p->lf.launches : p->ld.launches;
+}
+
+void partition_spmv_free(partition_spmv* p) { delete p; }
 
 // ------------------------------------------------------------------------------------------
 // raw SpMV: y = init + scale * A^T x

@@ -1,6 +1,7 @@
 // Internal declarations of the drivers (centrality.cu single GPU, mg.cu multi-GPU).
 #pragma once
 
+#include "epilogues.cuh"
 #include "graph.cuh"
 
 namespace b200 {
@@ -14,11 +15,21 @@ void eigenvector_centrality(b200_handle* h, b200_graph* g, const b200_eigenvecto
 void spmv_pull(b200_handle* h, b200_graph* g, int value_type, const void* x, double scale,
                double init, void* y);
 
+// one edge partition's SpMV with the raw epilogue (centrality.cu), used by the multi-GPU drivers
+struct partition_spmv;
+partition_spmv* partition_spmv_create(b200_handle* h, b200_graph* g, int part, int value_type);
+void partition_spmv_run(partition_spmv* p, const void* x, void* y, const iter_state* state);
+int64_t partition_spmv_launches(const partition_spmv* p);
+void partition_spmv_free(partition_spmv* p);
+
 // mg.cu
+void eigenvector_mg(b200_handle* h, b200_graph* g, const b200_eigenvector_params_t* p, void* out,
+                    b200_centrality_stats_t* stats);
 void pagerank_mg(b200_handle* h, b200_graph* g, const b200_pagerank_params_t* p, void* pageranks,
                  b200_centrality_stats_t* stats);
 void katz_mg(b200_handle* h, b200_graph* g, const b200_katz_params_t* p, void* out,
              b200_centrality_stats_t* stats);
+// graph_mg.cu
 void graph_create_mg(b200_handle* h, const void* src, const void* dst, const void* weights,
                      size_t ne, int vertex_type, int weight_type, const void* local_vertices,
                      size_t n_local_vertices, bool store_transposed, b200_graph* g);

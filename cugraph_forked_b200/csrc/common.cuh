@@ -146,6 +146,7 @@ struct b200_handle {
   size_t persisting_l2_max{0};
   // multi-GPU
   ncclComm_t world{nullptr}, row{nullptr}, col{nullptr};
+  cudaStream_t comm_stream{nullptr};   // per-partition reductions overlap the next SpMV
   int rank{0}, size{1};
   int row_size{1}, col_size{1};   // R, C
   int row_rank{0}, col_rank{0};   // rank inside row_comm / col_comm
@@ -174,6 +175,11 @@ struct edge_partition {
   int64_t num_chunks{0};          // kind-1 tiles
   dbuf<int64_t> long_row_chunk_first;  // [n_long + 1] prefix of chunk counts of the long rows
   int64_t num_long_rows{0};
+  // multi-GPU partitions: rows follow the GLOBAL degree order, so local degrees are not
+  // monotone; the schedule is then packed greedily and the long rows are listed by id
+  bool generic_schedule{false};
+  dbuf<int32_t> long_row_ids;     // [n_long] (generic schedule only; else rows [0, n_long))
+  int64_t zero_first{0};          // rows [zero_first, num_rows) have no edges
 };
 
 }  // namespace b200
@@ -190,6 +196,7 @@ struct b200_graph {
   int64_t num_edges{0};           // global
   int64_t local_first{0}, local_last{0};  // this rank's vertex partition
   std::vector<int64_t> vertex_partition_offsets;  // MG: size P+1
+  std::vector<std::vector<int64_t>> partition_segment_offsets;  // MG: one per edge partition
   b200::dbuf<char> renumber_map;  // vertex_type [local V]: internal -> external
   std::vector<b200::edge_partition> parts;  // SG: 1; MG: col_comm_size
   int64_t segment_offsets[8]{};

@@ -22,6 +22,12 @@ void graph_in_degrees(b200_handle* h, const b200_graph* g, void* out);
 void graph_ext_to_internal(b200_handle* h, b200_graph* g, const void* ext_ids, size_t n,
                            int32_t* out);
 void graph_transpose_storage(b200_handle* h, b200_graph* g);
+// multi-GPU counterpart (graph_mg.cu): local histograms + one reduction per row_comm peer
+void graph_out_weight_sums_mg(b200_handle* h, b200_graph* g);
+// helpers shared by the single- and multi-GPU builds (graph.cu)
+void launch_widen_ids(const void* a, const void* b, size_t n, int width, uint64_t* out,
+                      cudaStream_t s);
+int64_t launch_unique_ids(const uint64_t* sorted, size_t n, int width, void* out, cudaStream_t s);
 // (re)build the tile schedule of one edge partition: tiles of <= T edges and <= rowcap rows
 void build_schedule(b200_handle* h, edge_partition& ep, int T, int rowcap);
 

@@ -1,21 +1,685 @@
-// Multi-GPU (2D-partitioned) graph build and drivers.  Placeholder until the MG path lands.
+// Multi-GPU (2D-partitioned) power-iteration drivers.  One iteration, as the reference does it
+// (per_v_transform_reduce_incoming_outgoing_e.cuh:831-967, update_edge_src_dst_property.cuh:
+// 243-357, pagerank_impl.cuh:209-292):
+//   1. allgatherv of the local slice of the gathered vector over row_comm -> minor buffer
+//   2. for each of the C local edge partitions: the pull kernel with the raw epilogue, then
+//      ncclReduce of its result onto the col_comm rank that owns those majors; the reduction
+//      runs on a second stream so it overlaps the next partition's kernel
+//   3. one vertex pass over the local vertices (the driver's epilogue) + two scalars
+//      allreduced over all ranks; the stop test stays on the device, every rank sees the same
+//      scalars and therefore stops at the same iteration
+// Every rank calls these functions collectively with the same arguments.
+#include <cmath>
+#include <cstdlib>
+
 #include "centrality.cuh"
+#include "mg_comm.cuh"
+#include "prims.cuh"
 
 namespace b200 {
 
-void pagerank_mg(b200_handle*, b200_graph*, const b200_pagerank_params_t*, void*,
-                 b200_centrality_stats_t*)
+namespace {
+
+constexpr int kVT = 256;
+
+inline unsigned vgrid(size_t n, int sm_count)
 {
-  throw error(kNotImplemented, "multi-GPU PageRank is not implemented yet");
+  size_t b   = (n + kVT * 4 - 1) / (kVT * 4);
+  size_t cap = static_cast<size_t>(sm_count) * 8;
+  if (b > cap) b = cap;
+  if (b == 0) b = 1;
+  return static_cast<unsigned>(b);
 }
-void katz_mg(b200_handle*, b200_graph*, const b200_katz_params_t*, void*, b200_centrality_stats_t*)
+
+int env_int(const char* name, int dflt)
 {
-  throw error(kNotImplemented, "multi-GPU Katz centrality is not implemented yet");
+  const char* v = std::getenv(name);
+  return v ? std::atoi(v) : dflt;
 }
-void graph_create_mg(b200_handle*, const void*, const void*, const void*, size_t, int, int,
-                     const void*, size_t, bool, b200_graph*)
+
+template <typename RT>
+struct nccl_type;
+template <>
+struct nccl_type<float> {
+  static constexpr ncclDataType_t value = ncclFloat;
+};
+template <>
+struct nccl_type<double> {
+  static constexpr ncclDataType_t value = ncclDouble;
+};
+
+// ---- vertex passes ------------------------------------------------------------------------
+// partials layout: [2][gridDim.x]
+__device__ __forceinline__ void store_partials(double a, double b, double* partials, double* scratch)
 {
-  throw error(kNotImplemented, "multi-GPU graph creation is not implemented yet");
+  a = block_sum(a, scratch);
+  b = block_sum(b, scratch);
+  if (threadIdx.x == 0) {
+    partials[blockIdx.x]             = a;
+    partials[gridDim.x + blockIdx.x] = b;
+  }
+}
+
+template <typename RT, typename WT>
+__global__ void __launch_bounds__(kVT) mg_scale_kernel(const WT* outw, size_t n, RT alpha, RT* scale)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    RT w     = static_cast<RT>(outw[i]);
+    scale[i] = (w == RT(0)) ? RT(-1) : alpha / w;
+  }
+}
+
+template <typename RT>
+__global__ void __launch_bounds__(kVT) mg_sum_kernel(const RT* v, size_t n, double* partials)
+{
+  __shared__ double scratch[32];
+  double a = 0.0;
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    a += static_cast<double>(v[i]);
+  store_partials(a, 0.0, partials, scratch);
+}
+
+// out2[0] = sum partials[0][*], out2[1] = sum partials[1][*]  (zero once the loop is done)
+__global__ void __launch_bounds__(256) mg_fold_kernel(const double* partials, int n,
+                                                      const iter_state* st, double* out2)
+{
+  __shared__ double scratch[32];
+  double a = 0.0, b = 0.0;
+  if (!(st && st->done)) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      a += partials[i];
+      b += partials[n + i];
+    }
+  }
+  a = block_sum(a, scratch);
+  b = block_sum(b, scratch);
+  if (threadIdx.x == 0) {
+    out2[0] = a;
+    out2[1] = b;
+  }
+}
+
+// after the allreduce: publish the scalars and apply the stop test (same on every rank)
+__global__ void mg_commit_kernel(const double* in2, iter_state* st, double threshold,
+                                 int64_t iteration, int check, int which)
+{
+  if (st->done) return;
+  if (which & 1) st->a = in2[0];
+  if (which & 2) st->b = in2[1];
+  if (iteration > 0) st->iterations = iteration;
+  if (check && in2[1] < threshold) {
+    st->converged = 1;
+    st->done      = 1;
+  }
+}
+
+// pr = guess / sum (or 1 / V); x = pr * scale; partial a = dangling mass
+template <typename RT>
+__global__ void __launch_bounds__(kVT) mg_pagerank_init_kernel(RT* pr, const RT* scale, RT* x,
+                                                              size_t n, int has_guess,
+                                                              const iter_state* st, RT uniform,
+                                                              double* partials)
+{
+  __shared__ double scratch[32];
+  double dang = 0.0;
+  RT sum      = has_guess ? static_cast<RT>(st->a) : RT(1);
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    RT v  = has_guess ? pr[i] / sum : uniform;
+    pr[i] = v;
+    RT sc = scale[i];
+    if (sc < RT(0)) {
+      dang += static_cast<double>(v);
+      x[i] = RT(0);
+    } else {
+      x[i] = v * sc;
+    }
+  }
+  store_partials(dang, 0.0, partials, scratch);
+}
+
+// the PageRank epilogue of epilogues.cuh as a vertex pass (pagerank_impl.cuh:209-292)
+template <typename RT>
+__global__ void __launch_bounds__(kVT) mg_pagerank_update_kernel(
+  RT* pr, const RT* sum, const RT* scale, const RT* pers, RT* x, size_t n, const iter_state* st,
+  RT alpha, RT one_minus_alpha, RT num_vertices, double* partials)
+{
+  __shared__ double scratch[32];
+  double dang = 0.0, diff = 0.0;
+  if (!st->done) {
+    RT dangling  = static_cast<RT>(st->a);
+    RT base      = dangling * alpha + one_minus_alpha;
+    RT unvarying = pers ? RT(0) : base / num_vertices;
+    for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+         i += size_t(gridDim.x) * blockDim.x) {
+      RT v = sum[i] + unvarying;
+      if (pers) v += base * pers[i];
+      diff += fabs(static_cast<double>(v) - static_cast<double>(pr[i]));
+      pr[i] = v;
+      RT sc = scale[i];
+      if (sc < RT(0)) {
+        dang += static_cast<double>(v);
+        x[i] = RT(0);
+      } else {
+        x[i] = v * sc;
+      }
+    }
+  }
+  store_partials(dang, diff, partials, scratch);
+}
+
+// Katz (katz_centrality_impl.cuh:104-148): new = alpha * sum + beta; a = sum of squares
+template <typename RT>
+__global__ void __launch_bounds__(kVT) mg_katz_update_kernel(const RT* old_c, RT* new_c,
+                                                            const RT* sum, const RT* betas,
+                                                            size_t n, const iter_state* st,
+                                                            RT alpha, RT beta, double* partials)
+{
+  __shared__ double scratch[32];
+  double sq = 0.0, diff = 0.0;
+  if (!st->done) {
+    for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+         i += size_t(gridDim.x) * blockDim.x) {
+      RT v     = alpha * sum[i] + (betas ? betas[i] : beta);
+      new_c[i] = v;
+      diff += fabs(static_cast<double>(v) - static_cast<double>(old_c[i]));
+      sq += static_cast<double>(v) * static_cast<double>(v);
+    }
+  }
+  store_partials(sq, diff, partials, scratch);
+}
+
+template <typename RT>
+__global__ void __launch_bounds__(kVT) mg_sumsq_kernel(const RT* v, size_t n, const iter_state* st,
+                                                      double* partials)
+{
+  __shared__ double scratch[32];
+  double sq = 0.0;
+  if (!st->done) {
+    for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+         i += size_t(gridDim.x) * blockDim.x)
+      sq += static_cast<double>(v[i]) * static_cast<double>(v[i]);
+  }
+  store_partials(sq, 0.0, partials, scratch);
+}
+
+// eigenvector (eigenvector_centrality_impl.cuh:90-135): new = sum / ||sum||, b = |new - old|
+template <typename RT>
+__global__ void __launch_bounds__(kVT) mg_eigen_normalize_kernel(const RT* sum, const RT* old_c,
+                                                                RT* new_c, size_t n,
+                                                                const iter_state* st,
+                                                                double* partials)
+{
+  __shared__ double scratch[32];
+  double diff = 0.0;
+  if (!st->done) {
+    RT norm = static_cast<RT>(sqrt(st->a));
+    for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+         i += size_t(gridDim.x) * blockDim.x) {
+      RT v     = sum[i] / norm;
+      new_c[i] = v;
+      diff += fabs(static_cast<double>(v) - static_cast<double>(old_c[i]));
+    }
+  }
+  store_partials(0.0, diff, partials, scratch);
+}
+
+template <typename RT>
+__global__ void __launch_bounds__(kVT) mg_fill_kernel(RT* v, size_t n, RT x)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    v[i] = x;
+}
+
+template <typename RT>
+__global__ void __launch_bounds__(kVT) mg_divide_kernel(RT* v, size_t n, RT d)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x)
+    v[i] = v[i] / d;
+}
+
+template <typename RT>
+__global__ void __launch_bounds__(kVT) mg_scatter_pers_kernel(const int32_t* vertices,
+                                                             const RT* values, size_t n,
+                                                             RT pers_sum, int64_t first,
+                                                             int64_t nloc, RT* dense, int* bad)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    int64_t v = static_cast<int64_t>(vertices[i]) - first;
+    if (v < 0 || v >= nloc) { *bad = 1; continue; }
+    atomicAdd(&dense[v], values[i] / pers_sum);
+  }
+}
+
+// ---- the 2D exchange around the partitions' kernels -------------------------------------------
+template <typename RT>
+struct mg_engine {
+  b200_handle* h;
+  b200_graph* g;
+  int R, C;
+  size_t nloc, n_minor;
+  std::vector<partition_spmv*> parts;
+  std::vector<dbuf<RT>> partial;      // one result buffer per local edge partition
+  dbuf<RT> x_minor;                   // gathered vector over the local minor range
+  dbuf<RT> sum;                       // reduced result for the local vertices
+  std::vector<size_t> row_counts;     // vertex partition sizes of the row_comm peers
+  dbuf<iter_state> state;
+  dbuf<double> partials;              // [2][vg]
+  dbuf<double> scal;                  // 2 scalars in flight through the allreduce
+  unsigned vg;
+  std::vector<cudaEvent_t> ev_part;
+  cudaEvent_t ev_red{};
+  int64_t launches{0};
+  // device-time of the partitions' kernels on the main stream
+  std::vector<cudaEvent_t> ev_time;
+  int timed{0};
+
+  mg_engine(b200_handle* h_, b200_graph* g_) : h(h_), g(g_)
+  {
+    cudaStream_t s = h->stream;
+    R              = h->row_size;
+    C              = h->col_size;
+    nloc           = static_cast<size_t>(g->local_last - g->local_first);
+    n_minor        = static_cast<size_t>(g->parts[0].num_minors);
+    int vt         = sizeof(RT) == 4 ? B200_FLOAT32 : B200_FLOAT64;
+    parts.assign(C, nullptr);
+    for (int i = 0; i < C; ++i) parts[i] = partition_spmv_create(h, g, i, vt);
+    partial.resize(C);
+    for (int i = 0; i < C; ++i) partial[i].alloc(static_cast<size_t>(g->parts[i].num_rows), s, 8);
+    x_minor.alloc(n_minor, s, 8);
+    sum.alloc(nloc, s, 8);
+    auto const& vpo = g->vertex_partition_offsets;
+    row_counts.resize(R);
+    for (int j = 0; j < R; ++j)
+      row_counts[j] = static_cast<size_t>(vpo[h->col_rank * R + j + 1] - vpo[h->col_rank * R + j]);
+    state.alloc(1, s);
+    CUDA_TRY(cudaMemsetAsync(state.data(), 0, sizeof(iter_state), s));
+    vg = vgrid(nloc, h->sm_count);
+    partials.alloc(2 * vg, s);
+    scal.alloc(2, s);
+    ev_part.resize(C);
+    for (auto& e : ev_part) CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CUDA_TRY(cudaEventCreateWithFlags(&ev_red, cudaEventDisableTiming));
+  }
+  ~mg_engine()
+  {
+    for (auto p : parts) partition_spmv_free(p);
+    for (auto e : ev_part) cudaEventDestroy(e);
+    for (auto e : ev_time) cudaEventDestroy(e);
+    if (ev_red) cudaEventDestroy(ev_red);
+  }
+
+  // sum[local v] = sum over all edges into v of x[src], x given for the local vertices
+  void spmv(const RT* x_local)
+  {
+    cudaStream_t s = h->stream;
+    allgatherv(s, h->row, R, h->row_rank, x_local, x_minor.data(), row_counts, sizeof(RT));
+    const bool time_it = timed < 256;
+    if (time_it) {
+      cudaEvent_t a, b;
+      CUDA_TRY(cudaEventCreate(&a));
+      CUDA_TRY(cudaEventCreate(&b));
+      ev_time.push_back(a);
+      ev_time.push_back(b);
+      CUDA_TRY(cudaEventRecord(a, s));
+    }
+    for (int i = 0; i < C; ++i) {
+      partition_spmv_run(parts[i], x_minor.data(), partial[i].data(), state.data());
+      if (C == 1) break;
+      CUDA_TRY(cudaEventRecord(ev_part[i], s));
+      CUDA_TRY(cudaStreamWaitEvent(h->comm_stream, ev_part[i], 0));
+      size_t cnt = static_cast<size_t>(g->parts[i].num_rows);
+      if (cnt)
+        NCCL_TRY(ncclReduce(partial[i].data(), sum.data(), cnt, nccl_type<RT>::value, ncclSum, i,
+                            h->col, h->comm_stream));
+    }
+    if (time_it) {
+      CUDA_TRY(cudaEventRecord(ev_time[2 * timed + 1], s));
+      ++timed;
+    }
+    if (C > 1) {
+      CUDA_TRY(cudaEventRecord(ev_red, h->comm_stream));
+      CUDA_TRY(cudaStreamWaitEvent(s, ev_red, 0));
+    }
+  }
+  const RT* result() const { return C == 1 ? partial[0].data() : sum.data(); }
+
+  // scal = allreduce(fold(partials)); then commit into the state
+  void reduce_scalars(double threshold, int64_t iteration, bool check, int which)
+  {
+    cudaStream_t s = h->stream;
+    mg_fold_kernel<<<1, 256, 0, s>>>(partials.data(), static_cast<int>(vg), state.data(), scal.data());
+    CUDA_TRY(cudaGetLastError());
+    if (h->size > 1)
+      NCCL_TRY(ncclAllReduce(scal.data(), scal.data(), 2, ncclDouble, ncclSum, h->world, s));
+    mg_commit_kernel<<<1, 1, 0, s>>>(scal.data(), state.data(), threshold, iteration, check ? 1 : 0,
+                                     which);
+    CUDA_TRY(cudaGetLastError());
+    launches += 2;
+  }
+
+  iter_state read_state()
+  {
+    iter_state hs;
+    CUDA_TRY(cudaMemcpyAsync(&hs, state.data(), sizeof hs, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return hs;
+  }
+
+  void fill_stats(b200_centrality_stats_t* st, iter_state const& hs, double ms)
+  {
+    if (!st) return;
+    st->iterations   = hs.iterations;
+    st->converged    = hs.converged;
+    st->last_diff    = hs.b;
+    st->elapsed_ms   = ms;
+    int64_t l        = launches;
+    for (auto p : parts) l += partition_spmv_launches(p);
+    st->gpu_launches = l;
+    double tot       = 0.0;
+    for (int i = 0; i < timed; ++i) {
+      float t = 0.f;
+      cudaEventElapsedTime(&t, ev_time[2 * i], ev_time[2 * i + 1]);
+      tot += t;
+    }
+    st->spmv_ms       = tot;
+    st->spmv_launches = timed;
+  }
+};
+
+struct scoped_timer {
+  cudaEvent_t e0{}, e1{};
+  cudaStream_t s;
+  explicit scoped_timer(cudaStream_t s_) : s(s_)
+  {
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    cudaEventRecord(e0, s);
+  }
+  ~scoped_timer()
+  {
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+  }
+  double stop()
+  {
+    cudaEventRecord(e1, s);
+    cudaEventSynchronize(e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    return ms;
+  }
+};
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------
+// PageRank
+// ------------------------------------------------------------------------------------------
+template <typename RT>
+static void pagerank_mg_t(b200_handle* h, b200_graph* g, const b200_pagerank_params_t* p, RT* pr_user,
+                          b200_centrality_stats_t* stats)
+{
+  cudaStream_t s    = h->stream;
+  const RT alpha    = static_cast<RT>(p->alpha);
+  const RT epsilon  = static_cast<RT>(p->epsilon);
+  const bool fixed  = p->fixed_iterations > 0;
+  const int64_t cap = fixed ? p->fixed_iterations
+                            : std::max<int64_t>(1, static_cast<int64_t>(p->max_iterations));
+  if (stats) *stats = b200_centrality_stats_t{};
+  if (g->num_vertices == 0) return;
+
+  mg_engine<RT> E(h, g);
+  const size_t n = E.nloc;
+  dbuf<RT> scale(n, s, 8), pr(n, s, 8), x(n, s, 8);
+  if (p->has_initial_guess && n)
+    CUDA_TRY(cudaMemcpyAsync(pr.data(), pr_user, n * sizeof(RT), cudaMemcpyDeviceToDevice, s));
+  if (p->precomputed_out_weight_sums) {
+    mg_scale_kernel<RT, RT><<<E.vg, kVT, 0, s>>>(
+      static_cast<const RT*>(p->precomputed_out_weight_sums), n, alpha, scale.data());
+  } else {
+    graph_out_weight_sums(h, g);
+    mg_scale_kernel<RT, double><<<E.vg, kVT, 0, s>>>(g->out_weight_sums.data(), n, alpha, scale.data());
+  }
+  CUDA_TRY(cudaGetLastError());
+
+  // personalization: the caller's pairs are for vertices of this rank's partition (global
+  // internal ids); the normalising sum is global (pagerank_impl.cuh:111-150)
+  dbuf<RT> pers;
+  const bool has_pers_arg = p->personalization_vertices != nullptr;
+  if (has_pers_arg)
+    B200_EXPECTS(p->personalization_values != nullptr, kInvalidInput,
+                 "Invalid input argument: if personalization_vertices.has_value() is true, "
+                 "personalization_values.has_value() and personalization_vector_size.has_value() "
+                 "should be true as well.");
+  // every rank takes the same branch: the vector is in use when any rank passes entries
+  int64_t np_global = 0;
+  {
+    std::vector<int64_t> all =
+      allgather_host(h, h->world, h->size, {static_cast<int64_t>(p->personalization_size)});
+    for (int64_t v : all) np_global += v;
+  }
+  const bool personalized = np_global > 0;
+  if (personalized) {
+    size_t np = static_cast<size_t>(p->personalization_size);
+    unsigned pg = vgrid(np, h->sm_count);
+    dbuf<double> pparts(2 * std::max(pg, E.vg), s);
+    mg_sum_kernel<RT><<<pg, kVT, 0, s>>>(static_cast<const RT*>(p->personalization_values), np,
+                                         pparts.data());
+    mg_fold_kernel<<<1, 256, 0, s>>>(pparts.data(), static_cast<int>(pg), nullptr, E.scal.data());
+    CUDA_TRY(cudaGetLastError());
+    if (h->size > 1)
+      NCCL_TRY(ncclAllReduce(E.scal.data(), E.scal.data(), 2, ncclDouble, ncclSum, h->world, s));
+    double h2[2];
+    CUDA_TRY(cudaMemcpyAsync(h2, E.scal.data(), 16, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    RT pers_sum = static_cast<RT>(h2[0]);
+    B200_EXPECTS(pers_sum > RT(0), kInvalidInput,
+                 "Invalid input argument: sum of personalization valuese should be positive.");
+    pers.alloc(n, s);
+    CUDA_TRY(cudaMemsetAsync(pers.data(), 0, std::max<size_t>(n, 1) * sizeof(RT), s));
+    dbuf<int> bad(1, s);
+    CUDA_TRY(cudaMemsetAsync(bad.data(), 0, 4, s));
+    if (np) {
+      mg_scatter_pers_kernel<RT><<<pg, kVT, 0, s>>>(
+        static_cast<const int32_t*>(p->personalization_vertices),
+        static_cast<const RT*>(p->personalization_values), np, pers_sum, g->local_first,
+        static_cast<int64_t>(n), pers.data(), bad.data());
+      CUDA_TRY(cudaGetLastError());
+    }
+    int h_bad = 0;
+    CUDA_TRY(cudaMemcpyAsync(&h_bad, bad.data(), 4, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    std::vector<int64_t> flags = allgather_host(h, h->world, h->size, {static_cast<int64_t>(h_bad)});
+    for (int64_t f : flags)
+      B200_EXPECTS(!f, kInvalidInput,
+                   "Invalid input argument: peresonalization vertices have invalid vertex IDs.");
+  }
+
+  // initial values
+  if (p->has_initial_guess) {
+    mg_sum_kernel<RT><<<E.vg, kVT, 0, s>>>(pr.data(), n, E.partials.data());
+    CUDA_TRY(cudaGetLastError());
+    E.reduce_scalars(0.0, 0, false, 1);
+    iter_state hs = E.read_state();
+    B200_EXPECTS(static_cast<RT>(hs.a) > RT(0), kInvalidInput,
+                 "Invalid input argument: sum of the PageRank initial guess values should be "
+                 "positive.");
+  }
+  mg_pagerank_init_kernel<RT><<<E.vg, kVT, 0, s>>>(
+    pr.data(), scale.data(), x.data(), n, p->has_initial_guess ? 1 : 0, E.state.data(),
+    RT(1) / static_cast<RT>(g->num_vertices), E.partials.data());
+  CUDA_TRY(cudaGetLastError());
+  E.reduce_scalars(0.0, 0, false, 1);
+
+  const int check_every = std::max(1, env_int("B200_CHECK_EVERY", 8));
+  scoped_timer timer(s);
+  iter_state hs{};
+  for (int64_t it = 0; it < cap; ++it) {
+    E.spmv(x.data());
+    mg_pagerank_update_kernel<RT><<<E.vg, kVT, 0, s>>>(
+      pr.data(), E.result(), scale.data(), personalized ? pers.data() : nullptr, x.data(), n,
+      E.state.data(), alpha, static_cast<RT>(1.0 - p->alpha), static_cast<RT>(g->num_vertices),
+      E.partials.data());
+    CUDA_TRY(cudaGetLastError());
+    ++E.launches;
+    E.reduce_scalars(static_cast<double>(epsilon), it + 1, !fixed, 3);
+    if (!fixed && ((it + 1) % check_every == 0)) {
+      hs = E.read_state();
+      if (hs.done) break;
+    }
+  }
+  double ms = timer.stop();
+  hs        = E.read_state();
+  E.fill_stats(stats, hs, ms);
+  if (n) CUDA_TRY(cudaMemcpyAsync(pr_user, pr.data(), n * sizeof(RT), cudaMemcpyDeviceToDevice, s));
+  CUDA_TRY(cudaStreamSynchronize(s));
+  if (!fixed && !hs.converged) throw error(kUnknownError, "PageRank failed to converge.");
+}
+
+void pagerank_mg(b200_handle* h, b200_graph* g, const b200_pagerank_params_t* p, void* pageranks,
+                 b200_centrality_stats_t* stats)
+{
+  B200_EXPECTS(h->world != nullptr, kInvalidHandle, "multi-GPU PageRank needs an MG handle");
+  if (p->value_type == B200_FLOAT32)
+    pagerank_mg_t<float>(h, g, p, static_cast<float*>(pageranks), stats);
+  else
+    pagerank_mg_t<double>(h, g, p, static_cast<double*>(pageranks), stats);
+}
+
+// ------------------------------------------------------------------------------------------
+// Katz centrality
+// ------------------------------------------------------------------------------------------
+template <typename RT>
+static void katz_mg_t(b200_handle* h, b200_graph* g, const b200_katz_params_t* p, RT* kc,
+                      b200_centrality_stats_t* stats)
+{
+  cudaStream_t s    = h->stream;
+  const bool fixed  = p->fixed_iterations > 0;
+  const int64_t cap = fixed ? p->fixed_iterations
+                            : std::max<int64_t>(1, static_cast<int64_t>(p->max_iterations));
+  if (stats) *stats = b200_centrality_stats_t{};
+  if (g->num_vertices == 0) return;
+  mg_engine<RT> E(h, g);
+  const size_t n = E.nloc;
+  dbuf<RT> work0(n, s, 8), work1(n, s, 8);
+  if (p->has_initial_guess && n)
+    CUDA_TRY(cudaMemcpyAsync(work0.data(), kc, n * sizeof(RT), cudaMemcpyDeviceToDevice, s));
+  else
+    CUDA_TRY(cudaMemsetAsync(work0.data(), 0, std::max<size_t>(n, 1) * sizeof(RT), s));
+  RT* buf[2] = {work0.data(), work1.data()};
+  const int check_every = std::max(1, env_int("B200_CHECK_EVERY", 8));
+  scoped_timer timer(s);
+  iter_state hs{};
+  for (int64_t it = 0; it < cap; ++it) {
+    RT* old_c = buf[it & 1];
+    RT* new_c = buf[(it + 1) & 1];
+    E.spmv(old_c);
+    mg_katz_update_kernel<RT><<<E.vg, kVT, 0, s>>>(
+      old_c, new_c, E.result(), static_cast<const RT*>(p->betas), n, E.state.data(),
+      static_cast<RT>(p->alpha), static_cast<RT>(p->beta), E.partials.data());
+    CUDA_TRY(cudaGetLastError());
+    ++E.launches;
+    E.reduce_scalars(static_cast<double>(static_cast<RT>(p->epsilon)), it + 1, !fixed, 3);
+    if (!fixed && ((it + 1) % check_every == 0)) {
+      hs = E.read_state();
+      if (hs.done) break;
+    }
+  }
+  double ms = timer.stop();
+  hs        = E.read_state();
+  E.fill_stats(stats, hs, ms);
+  if (!fixed && !hs.converged) throw error(kUnknownError, "Katz Centrality failed to converge.");
+  RT* result = buf[hs.iterations & 1];
+  if (n) CUDA_TRY(cudaMemcpyAsync(kc, result, n * sizeof(RT), cudaMemcpyDeviceToDevice, s));
+  if (p->normalize) {
+    RT l2 = static_cast<RT>(std::sqrt(static_cast<RT>(hs.a)));
+    B200_EXPECTS(l2 > RT(0), kUnknownError,
+                 "L2 norm of the computed Katz Centrality values should be positive.");
+    if (n) {
+      mg_divide_kernel<RT><<<E.vg, kVT, 0, s>>>(kc, n, l2);
+      CUDA_TRY(cudaGetLastError());
+    }
+  }
+  CUDA_TRY(cudaStreamSynchronize(s));
+}
+
+void katz_mg(b200_handle* h, b200_graph* g, const b200_katz_params_t* p, void* out,
+             b200_centrality_stats_t* stats)
+{
+  B200_EXPECTS(h->world != nullptr, kInvalidHandle, "multi-GPU Katz needs an MG handle");
+  if (p->value_type == B200_FLOAT32) katz_mg_t<float>(h, g, p, static_cast<float*>(out), stats);
+  else katz_mg_t<double>(h, g, p, static_cast<double*>(out), stats);
+}
+
+// ------------------------------------------------------------------------------------------
+// eigenvector centrality
+// ------------------------------------------------------------------------------------------
+template <typename RT>
+static void eigenvector_mg_t(b200_handle* h, b200_graph* g, const b200_eigenvector_params_t* p,
+                             RT* c, b200_centrality_stats_t* stats)
+{
+  cudaStream_t s    = h->stream;
+  const bool fixed  = p->fixed_iterations > 0;
+  const int64_t cap = fixed ? p->fixed_iterations
+                            : std::max<int64_t>(1, static_cast<int64_t>(p->max_iterations));
+  if (stats) *stats = b200_centrality_stats_t{};
+  if (g->num_vertices == 0) return;
+  mg_engine<RT> E(h, g);
+  const size_t n = E.nloc;
+  dbuf<RT> work0(n, s, 8), work1(n, s, 8);
+  if (p->has_initial_guess && n) {
+    CUDA_TRY(cudaMemcpyAsync(work0.data(), c, n * sizeof(RT), cudaMemcpyDeviceToDevice, s));
+  } else {
+    mg_fill_kernel<RT><<<E.vg, kVT, 0, s>>>(work0.data(), n, RT(1) / static_cast<RT>(g->num_vertices));
+    CUDA_TRY(cudaGetLastError());
+  }
+  RT* buf[2] = {work0.data(), work1.data()};
+  const double threshold =
+    static_cast<double>(static_cast<RT>(g->num_vertices) * static_cast<RT>(p->epsilon));
+  const int check_every = std::max(1, env_int("B200_CHECK_EVERY", 8));
+  scoped_timer timer(s);
+  iter_state hs{};
+  for (int64_t it = 0; it < cap; ++it) {
+    RT* old_c = buf[it & 1];
+    RT* new_c = buf[(it + 1) & 1];
+    E.spmv(old_c);
+    mg_sumsq_kernel<RT><<<E.vg, kVT, 0, s>>>(E.result(), n, E.state.data(), E.partials.data());
+    CUDA_TRY(cudaGetLastError());
+    E.reduce_scalars(0.0, 0, false, 1);
+    mg_eigen_normalize_kernel<RT><<<E.vg, kVT, 0, s>>>(E.result(), old_c, new_c, n, E.state.data(),
+                                                       E.partials.data());
+    CUDA_TRY(cudaGetLastError());
+    E.launches += 2;
+    E.reduce_scalars(threshold, it + 1, !fixed, 2);
+    if (!fixed && ((it + 1) % check_every == 0)) {
+      hs = E.read_state();
+      if (hs.done) break;
+    }
+  }
+  double ms = timer.stop();
+  hs        = E.read_state();
+  E.fill_stats(stats, hs, ms);
+  if (!fixed && !hs.converged)
+    throw error(kUnknownError, "Eigenvector Centrality failed to converge.");
+  RT* result = buf[hs.iterations & 1];
+  if (n) CUDA_TRY(cudaMemcpyAsync(c, result, n * sizeof(RT), cudaMemcpyDeviceToDevice, s));
+  CUDA_TRY(cudaStreamSynchronize(s));
+}
+
+void eigenvector_mg(b200_handle* h, b200_graph* g, const b200_eigenvector_params_t* p, void* out,
+                    b200_centrality_stats_t* stats)
+{
+  B200_EXPECTS(h->world != nullptr, kInvalidHandle, "multi-GPU eigenvector needs an MG handle");
+  if (p->value_type == B200_FLOAT32)
+    eigenvector_mg_t<float>(h, g, p, static_cast<float*>(out), stats);
+  else
+    eigenvector_mg_t<double>(h, g, p, static_cast<double*>(out), stats);
 }
 
 }  // namespace b200

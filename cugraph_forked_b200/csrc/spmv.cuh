@@ -174,8 +174,8 @@ __global__ void __launch_bounds__(kPullThreads, 1)
           }
         }
         mbar_arrive_expect_tx(&full_bar[s], bytes + off_bytes + EPI::kStage * in_bytes);
-        bulk_g2s(idx_s(s), P.indices + a0, cnt * 4u, &full_bar[s], pol_stream);
-        if (WEIGHTED)
+        if (cnt) bulk_g2s(idx_s(s), P.indices + a0, cnt * 4u, &full_bar[s], pol_stream);
+        if (WEIGHTED && cnt)
           bulk_g2s(w_s(s), weights + a0, cnt * static_cast<uint32_t>(sizeof(RT)), &full_bar[s],
                    pol_stream);
         if (off_bytes) bulk_g2s(off_s(s), offsets + r0, off_bytes, &full_bar[s], pol_stream);
@@ -348,6 +348,7 @@ __global__ void __launch_bounds__(kPullThreads, 1)
 // state and applies the driver's stop test.
 // ------------------------------------------------------------------------------------------
 struct tail_params {
+  const int32_t* long_row_ids;          // [n_long] row of every long row, or nullptr = identity
   const int64_t* long_row_chunk_first;  // [n_long + 1]
   const double* chunk_partials;
   int64_t num_long_rows;
@@ -380,15 +381,17 @@ __global__ void __launch_bounds__(THREADS) pull_tail_kernel(const __grid_constan
     const int64_t r = k * groups_total + static_cast<int64_t>(blockIdx.x) * (THREADS / G) + tid / G;
     const bool act  = r < P.num_long_rows;
     double s        = 0.0;
+    int64_t row     = r;
     typename EPI::pre_t pre{};
     if (act) {
       const int64_t c0 = P.long_row_chunk_first[r], c1 = P.long_row_chunk_first[r + 1];
-      if (l == 0) pre = epi.prefetch(r);
+      if (P.long_row_ids) row = P.long_row_ids[r];
+      if (l == 0) pre = epi.prefetch(row);
       for (int64_t c = c0 + l; c < c1; c += G) s += P.chunk_partials[c];
     }
 #pragma unroll
     for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o, G);
-    if (act && l == 0) epi.finish(r, static_cast<RT>(s), pre, acc);
+    if (act && l == 0) epi.finish(row, static_cast<RT>(s), pre, acc);
   }
   (void)lane; (void)warp;
   if (!P.cta_partials) return;

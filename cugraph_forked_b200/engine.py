@@ -159,17 +159,34 @@ class Graph:
         v = self.view()
         return [int(v.segment_offsets[i]) for i in range(v.num_segments + 1)] if v.num_segments else []
 
+    def vertex_partition_offsets(self) -> list[int]:
+        n = self.handle.world_size if self.multi_gpu else 1
+        buf = (ctypes.c_int64 * (n + 1))()
+        check(_lib.lib().b200_graph_vertex_partition_offsets(self._g, buf))
+        return [int(x) for x in buf]
+
+    def partition_segment_offsets(self, partition: int) -> list[int]:
+        v = self.view(partition)
+        return [int(v.segment_offsets[i]) for i in range(v.num_segments + 1)]
+
     def offsets(self, partition=None) -> torch.Tensor:
         v = self.view(partition)
-        return self._copy(v.offsets, v.num_vertices + 1, _TD[v.edge_type])
+        n = (v.major_last - v.major_first) if partition is not None else v.num_vertices
+        return self._copy(v.offsets, n + 1, _TD[v.edge_type])
+
+    def _part_edges(self, partition) -> int:
+        # the partition view reports the partition's own edge count
+        return self.view(partition).num_edges
 
     def indices(self, partition=None) -> torch.Tensor:
+        """minor OFFSETS (global minor id - view.minor_first), ascending inside every row"""
         v = self.view(partition)
-        return self._copy(v.indices, v.num_edges, torch.int32)
+        return self._copy(v.indices, self._part_edges(partition), torch.int32)
 
     def weights(self, partition=None):
         v = self.view(partition)
-        return None if not v.weights else self._copy(v.weights, v.num_edges, _TD[v.weight_type])
+        return None if not v.weights else self._copy(v.weights, self._part_edges(partition),
+                                                     _TD[v.weight_type])
 
     def renumber_map(self) -> torch.Tensor:
         v = self.view()

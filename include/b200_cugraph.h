@@ -82,6 +82,9 @@ typedef struct b200_graph_view {
   /* multi-GPU only (zero / NULL on a single GPU) */
   int32_t comm_rank, comm_size, row_comm_size, col_comm_size;
   int64_t local_vertex_first, local_vertex_last; /* this rank's vertex partition (internal ids) */
+  /* ranges of this edge partition (graph_view.hpp:181-212); [0, V) on a single GPU.  `indices`
+   * hold minor OFFSETS (global minor id - minor_first), the form the kernel gathers with. */
+  int64_t major_first, major_last, minor_first, minor_last;
 } b200_graph_view_t;
 
 /* Single-GPU graph from a COO edge list (external ids).  vertices may be NULL (vertex set =
@@ -103,6 +106,8 @@ int b200_graph_create_mg(b200_handle_t* h, const void* src, const void* dst, con
 int b200_graph_view(const b200_graph_t* g, b200_graph_view_t* out);
 /* view of local edge partition i (0 <= i < col_comm_size) of a multi-GPU graph */
 int b200_graph_partition_view(const b200_graph_t* g, int i, b200_graph_view_t* out);
+/* partition_t::vertex_partition_range_offsets (graph_view.hpp:121-170): out[comm_size + 1] */
+int b200_graph_vertex_partition_offsets(const b200_graph_t* g, int64_t* out);
 void b200_graph_free(b200_graph_t* g);
 
 /* graph_view_t::compute_out_weight_sums (cpp/src/structure/graph_view_impl.cuh:238-265,

@@ -150,6 +150,99 @@ def out_weight_sums(indices, weights, num_minors, dtype):
 
 
 # ----------------------------------------------------------------------------------------------
+# multi-GPU build on VIRTUAL ranks  (create_graph_from_edgelist_impl.cuh:207-555,
+# renumber_edgelist_impl.cuh:665-921, graph_view.hpp:81-242)
+# ----------------------------------------------------------------------------------------------
+def rank_coords(rank: int, row_comm_size: int) -> tuple[int, int]:
+    """(row_comm_rank, col_comm_rank) of a world rank: ranks of one row communicator are
+    consecutive (partition_manager.hpp:92-100: row colour = rank / R, col colour = rank % R)."""
+    return rank % row_comm_size, rank // row_comm_size
+
+
+def build_mg(src, dst, weights, comm_size, store_transposed=True, vertices=None):
+    """What every rank of a P = R x C grid holds after cugraph_mg_graph_create, computed on one
+    host.  Returns a dict:
+      R, C, num_vertices, vertex_partition_offsets [P+1]
+      labels[r]            renumber_map_labels of rank r (external ids in new-id order)
+      segment_offsets[r]   vertex-partition segment offsets of rank r (thresholds scaled by C,
+                           renumber_edgelist_impl.cuh:394-449)
+      edge_rank            owner rank of every input edge (graph_utils.cuh:69-82)
+      new_major, new_minor renumbered endpoints of every input edge
+      parts[g][i]          edge partition i of rank g: offsets (full, not DCSC-compressed),
+                           indices (GLOBAL minor ids, ascending per row), weights, major_first,
+                           major_last, minor_first, minor_last, segment_offsets
+    Edge partition i of rank g holds the edges whose major is owned by rank R*i + row_rank(g)
+    (graph_view.hpp:181-189) and whose minor is owned by a rank of column col_rank(g)
+    (:204-212)."""
+    P = int(comm_size)
+    R, C = grid_2d(P)
+    majors, minors = (dst, src) if store_transposed else (src, dst)
+    majors = np.asarray(majors)
+    minors = np.asarray(minors)
+    if vertices is None:
+        all_v = np.unique(np.concatenate([majors, minors]))
+    else:
+        all_v = np.unique(np.asarray(vertices, majors.dtype))
+    owner = gpu_id_from_ext_vertex(all_v, P) if len(all_v) else np.zeros(0, np.int32)
+    pos_major = np.searchsorted(all_v, majors)
+    pos_minor = np.searchsorted(all_v, minors)
+    degrees = np.bincount(pos_major, minlength=len(all_v)).astype(np.int64)
+    thresholds = segment_thresholds(C)
+    labels, segs, counts = [], [], []
+    new_of = np.zeros(len(all_v), dtype=np.int64)
+    first = 0
+    for r in range(P):
+        sel = np.nonzero(owner == r)[0]          # ascending external id
+        lab, _, seg = sort_by_degree_and_segment(all_v[sel], degrees[sel], thresholds)
+        order = np.argsort(-degrees[sel], kind="stable")
+        new_of[sel[order]] = first + np.arange(len(sel))
+        labels.append(lab.astype(majors.dtype))
+        segs.append(seg)
+        counts.append(len(sel))
+        first += len(sel)
+    vpo = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+    new_major = new_of[pos_major]
+    new_minor = new_of[pos_minor]
+    edge_rank = (gpu_id_from_ext_edge_endpoints(majors, minors, P, R, C)
+                 if len(majors) else np.zeros(0, np.int32))
+    major_owner = owner[pos_major] if len(majors) else np.zeros(0, np.int32)
+    parts = []
+    for g in range(P):
+        row_rank, col_rank = rank_coords(g, R)
+        mine = edge_rank == g
+        minor_first, minor_last = int(vpo[col_rank * R]), int(vpo[(col_rank + 1) * R])
+        plist = []
+        for i in range(C):
+            vp = R * i + row_rank
+            sel = np.nonzero(mine & (major_owner == vp))[0]
+            mf, ml = int(vpo[vp]), int(vpo[vp + 1])
+            w = None if weights is None else np.asarray(weights)[sel]
+            offsets, indices, ww = compress_sorted(new_major[sel], new_minor[sel], w, mf, ml)
+            assert len(indices) == 0 or (indices.min() >= minor_first and indices.max() < minor_last)
+            plist.append(dict(offsets=offsets, indices=indices, weights=ww, major_first=mf,
+                              major_last=ml, minor_first=minor_first, minor_last=minor_last,
+                              segment_offsets=segs[vp]))
+        parts.append(plist)
+    return dict(R=R, C=C, num_vertices=int(vpo[-1]), vertex_partition_offsets=vpo, labels=labels,
+                segment_offsets=segs, edge_rank=edge_rank, new_major=new_major,
+                new_minor=new_minor, parts=parts)
+
+
+def compress_hypersparse(offsets, major_first, segment_offsets):
+    """compress_hypersparse_offsets, structure_utils.cuh:109-159: rows at or after the start of the
+    hypersparse segment keep only their non-empty entries.  Returns (dcs_offsets,
+    dcs_nzd_vertices) or None when the vertex partition has no hypersparse segment
+    (segment_offsets has 5 entries + end only when col_comm_size >= 2)."""
+    if len(segment_offsets) != 6:
+        return None
+    hs_first = segment_offsets[3]
+    deg = np.diff(offsets)
+    nz = np.nonzero(deg[hs_first:] > 0)[0] + hs_first
+    dcs_offsets = np.concatenate([offsets[:hs_first + 1], offsets[nz + 1]])
+    return dcs_offsets, (nz + major_first)
+
+
+# ----------------------------------------------------------------------------------------------
 # R-MAT  (cpp/src/generators/generate_rmat_edgelist.cu:35-111)
 # ----------------------------------------------------------------------------------------------
 def splitmix64(x: np.ndarray) -> np.ndarray:
