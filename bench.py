@@ -265,6 +265,17 @@ def run_b200(args, rank, world):
                "what": "host COO (pinned) -> H2D -> graph build -> K iterations -> D2H of "
                        "(vertex ids, scores); bytes are per-call totals / K"}
 
+    # ---- collectives of one iteration: allgatherv over row_comm lands
+    #      (R-1)/R * V/C values per GPU, the per-partition reductions over col_comm send
+    #      (C-1)/C * V/R values per GPU; fraction of one NVLink direction (900 GB/s) they would
+    #      need if they were not overlapped with the kernels ----
+    nvlink = None
+    if world > 1:
+        recv_b = (rows - 1) / rows * (nv / cols) * val_size
+        send_b = (cols - 1) / cols * (nv / rows) * val_size
+        step_s = ms_total / args.steps / 1e3
+        nvlink = {"allgather_recv_bytes_per_gpu": int(recv_b), "reduce_send_bytes_per_gpu": int(send_b),
+                  "frac_of_900GBps_per_direction": max(recv_b, send_b) / step_s / 900e9}
     if rank != 0:
         return
     cpu = None
@@ -290,6 +301,8 @@ def run_b200(args, rank, world):
                          if ms_total > 0 else None},
         "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": st.gpu_launches, "clocks": clocks,
     }
+    if nvlink:
+        line["nvlink"] = nvlink
     print(json.dumps(line), flush=True)
 
 
