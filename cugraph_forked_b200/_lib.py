@@ -10,7 +10,9 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcugraph_b200.so")
+# B200_LIBRARY points tuning sweeps at a variant build (scripts/build_variant.sh); it is still
+# this library, compiled with other constants - never a fallback
+LIB_PATH = os.environ.get("B200_LIBRARY") or os.path.join(_HERE, "libcugraph_b200.so")
 
 INT32, INT64, FLOAT32, FLOAT64 = 0, 1, 2, 3
 

@@ -36,7 +36,7 @@ struct pull_cfg {
 };
 template <typename RT, bool WEIGHTED>
 struct default_cfg {
-  using type = pull_cfg<4096, 3, 1024>;  // f32 unweighted (best of the sweep in profiles/)
+  using type = pull_cfg<4096, 4, 512>;  // f32 unweighted (best of the sweep in profiles/)
 };
 template <>
 struct default_cfg<float, true> {
@@ -53,13 +53,13 @@ struct default_cfg<double, true> {
 // alternatives for tuning sweeps (B200_PULL_CFG=1..), f32 unweighted int32 offsets only
 template <int ID>
 struct alt_cfg {
-  using type = pull_cfg<4096, 3, 1024>;
+  using type = pull_cfg<4096, 4, 512>;
 };
-template <> struct alt_cfg<1> { using type = pull_cfg<2048, 6, 512>; };
+template <> struct alt_cfg<1> { using type = pull_cfg<4096, 3, 1024>; };
 template <> struct alt_cfg<2> { using type = pull_cfg<4096, 4, 1024>; };
-template <> struct alt_cfg<3> { using type = pull_cfg<2048, 4, 512>; };
-template <> struct alt_cfg<4> { using type = pull_cfg<2048, 8, 512>; };
-template <> struct alt_cfg<5> { using type = pull_cfg<1024, 8, 256>; };
+template <> struct alt_cfg<3> { using type = pull_cfg<4096, 3, 512>; };
+template <> struct alt_cfg<4> { using type = pull_cfg<4096, 5, 512>; };
+template <> struct alt_cfg<5> { using type = pull_cfg<8192, 2, 1024>; };
 constexpr int kNumAltCfg = 6;
 
 int env_int(const char* name, int dflt)
@@ -950,3 +950,14 @@ void spmv_pull(b200_handle* h, b200_graph* g, int value_type, const void* x, dou
 }
 
 }  // namespace b200
+
+#ifdef B200_PROFILE_ROLES
+// tuning builds only (scripts/build_variant.sh prof -DB200_PROFILE_ROLES)
+extern "C" int b200_debug_role_clocks(unsigned long long* out)
+{
+  return cudaMemcpyFromSymbol(out, b200::b200_role_clocks, sizeof(unsigned long long) * 256 * 8) ==
+             cudaSuccess
+           ? 0
+           : 1;
+}
+#endif

@@ -54,11 +54,27 @@ struct pull_params {
   const iter_state* state; // may be nullptr (raw spmv)
 };
 
+#ifdef B200_PROFILE_ROLES
+// tuning builds only: clocks one lane of each role spends waiting / working, per CTA
+//  [0] kernel  [1] gather wait full  [2] gather zero rows  [3] reduce wait full
+//  [4] reduce wait ready  [5] producer wait empty  [6] tiles  [7] gather retire stalls (unused)
+__device__ unsigned long long b200_role_clocks[256][8];
+#define B200_CLK(var) const long long var = clock64()
+#define B200_ACC(acc, t0) acc += clock64() - (t0)
+#else
+#define B200_CLK(var)
+#define B200_ACC(acc, t0)
+#endif
+
 constexpr int kLongRowDegree = 1024;  // = mid_degree_threshold, graph_view.hpp:255-263
 
-constexpr int kGatherWarps  = 16;
-constexpr int kReduceWarps  = 15;
-constexpr int kPullThreads  = 1024;  // 16 gather + 15 reduce + 1 producer warp
+// tuning builds override the warp split (scripts/build_variant.sh); 31 worker warps in total
+#ifndef B200_GATHER_WARPS
+#define B200_GATHER_WARPS 16
+#endif
+constexpr int kGatherWarps  = B200_GATHER_WARPS;
+constexpr int kReduceWarps  = 31 - kGatherWarps;
+constexpr int kPullThreads  = 1024;  // gather + reduce + 1 producer warp
 constexpr int kGatherThreads = kGatherWarps * 32;
 constexpr int kReduceThreads = kReduceWarps * 32;
 
@@ -72,7 +88,8 @@ struct pull_smem {
   static constexpr size_t w_b    = WEIGHTED ? size_t(cap) * sizeof(RT) : 0;
   static constexpr size_t off_b  = size_t(ROWCAP + 8) * sizeof(ET);
   static constexpr size_t in_b   = size_t(ROWCAP + 8) * sizeof(RT);  // one staged epilogue input
-  static constexpr size_t stage  = ((idx_b + w_b + off_b + NSTAGED * in_b) + 127) & ~size_t(127);
+  static constexpr size_t desc_b = 32;  // the tile descriptor travels with the tile (TMA)
+  static constexpr size_t stage  = ((idx_b + w_b + off_b + NSTAGED * in_b + desc_b) + 127) & ~size_t(127);
   // 4-byte results overwrite the staged indices in place; 8-byte results get their own ring
   static constexpr bool inplace  = sizeof(RT) == 4;
   static constexpr size_t prod_b = inplace ? 0 : ((size_t(cap) * sizeof(RT) + 127) & ~size_t(127));
@@ -98,6 +115,10 @@ __global__ void __launch_bounds__(kPullThreads, 1)
   __shared__ double red_a[32], red_b[32];
 
   if (P.state && P.state->done) return;
+#ifdef B200_PROFILE_ROLES
+  const long long prof_t0 = clock64();
+  long long prof_a = 0, prof_b = 0;
+#endif
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int hub_n           = P.hub_entries;
@@ -113,6 +134,10 @@ __global__ void __launch_bounds__(kPullThreads, 1)
   auto in_s = [&](int s, int k) {
     return reinterpret_cast<RT*>(ring_base + s * S::stage + S::idx_b + S::w_b + S::off_b +
                                  k * S::in_b);
+  };
+  auto desc_s = [&](int s) {
+    return reinterpret_cast<tile_t*>(ring_base + s * S::stage + S::idx_b + S::w_b + S::off_b +
+                                     EPI::kStage * S::in_b);
   };
   auto prod_s = [&](int s) {
     return S::inplace ? reinterpret_cast<RT*>(ring_base + s * S::stage)
@@ -147,111 +172,163 @@ __global__ void __launch_bounds__(kPullThreads, 1)
     if (lane == 0) {
       const uint64_t pol_stream = policy_evict_first();
       const uint64_t pol_keep   = policy_evict_last();
-      for (int64_t j = 0; j < my_n; ++j) {
-        const int s = static_cast<int>(j % STAGES);
-        if (j >= STAGES) mbar_wait(&empty_bar[s], static_cast<uint32_t>(((j / STAGES) - 1) & 1));
-        fence_proxy_async();
-        const tile_t t     = P.tiles[blockIdx.x + j * stride];
-        const int lead     = static_cast<int>(t.edge_first & 3);
-        const int64_t a0   = t.edge_first - lead;
-        const uint32_t cnt = static_cast<uint32_t>((lead + t.num_edges + 3) & ~3);
-        uint32_t bytes     = cnt * 4u;
-        if (WEIGHTED) bytes += cnt * static_cast<uint32_t>(sizeof(RT));
-        uint32_t off_bytes = 0, in_bytes = 0;
-        int64_t r0 = 0, q0 = 0;
+      // Per tile: what to copy and from where.  The descriptor of tile j + 1 is read while tile
+      // j's copies are issued, and every descriptor is also written into its stage, so the
+      // other warps never touch global memory for it.
+      struct span_t {
+        int64_t a0, r0, q0;
+        uint32_t cnt, off_bytes, in_bytes;
+      };
+      auto spans = [&](tile_t const& t) {
+        span_t sp{};
+        const int lead = static_cast<int>(t.edge_first & 3);
+        sp.a0          = t.edge_first - lead;
+        sp.cnt         = static_cast<uint32_t>((lead + t.num_edges + 3) & ~3);
         if (t.kind == 0) {
           constexpr int per16 = 16 / sizeof(ET);
-          r0                  = t.row_first & ~int64_t(per16 - 1);
-          int n_off           = static_cast<int>(t.row_first - r0) + t.num_rows + 1;
+          sp.r0               = t.row_first & ~int64_t(per16 - 1);
+          int n_off           = static_cast<int>(t.row_first - sp.r0) + t.num_rows + 1;
           n_off               = (n_off + per16 - 1) & ~(per16 - 1);
-          off_bytes           = static_cast<uint32_t>(n_off * sizeof(ET));
+          sp.off_bytes        = static_cast<uint32_t>(n_off * sizeof(ET));
           if (EPI::kStage > 0) {
             constexpr int q16 = 16 / sizeof(RT);
-            q0                = t.row_first & ~int64_t(q16 - 1);
-            int n_in          = static_cast<int>(t.row_first - q0) + t.num_rows;
+            sp.q0             = t.row_first & ~int64_t(q16 - 1);
+            int n_in          = static_cast<int>(t.row_first - sp.q0) + t.num_rows;
             n_in              = (n_in + q16 - 1) & ~(q16 - 1);
-            in_bytes          = static_cast<uint32_t>(n_in * sizeof(RT));
+            sp.in_bytes       = static_cast<uint32_t>(n_in * sizeof(RT));
           }
         }
-        mbar_arrive_expect_tx(&full_bar[s], bytes + off_bytes + EPI::kStage * in_bytes);
-        if (cnt) bulk_g2s(idx_s(s), P.indices + a0, cnt * 4u, &full_bar[s], pol_stream);
-        if (WEIGHTED && cnt)
-          bulk_g2s(w_s(s), weights + a0, cnt * static_cast<uint32_t>(sizeof(RT)), &full_bar[s],
+        return sp;
+      };
+      // (an L2 bulk prefetch several tiles ahead was tried and measured neutral to negative:
+      // the ring is not bound by DRAM latency but by per-operation issue cost, so the
+      // producer issues as few asynchronous operations per tile as possible)
+      auto tile_at = [&](int64_t j) { return P.tiles[blockIdx.x + j * stride]; };
+      tile_t t = my_n > 0 ? tile_at(0) : tile_t{};
+      for (int64_t j = 0; j < my_n; ++j) {
+        const int s = static_cast<int>(j % STAGES);
+        tile_t tn = t;
+        if (j + 1 < my_n) tn = tile_at(j + 1);
+        {
+          B200_CLK(w0);
+          if (j >= STAGES) mbar_wait(&empty_bar[s], static_cast<uint32_t>(((j / STAGES) - 1) & 1));
+          B200_ACC(prof_a, w0);
+        }
+        fence_proxy_async();
+        const span_t sp = spans(t);
+        uint32_t bytes  = sp.cnt * 4u;
+        if (WEIGHTED) bytes += sp.cnt * static_cast<uint32_t>(sizeof(RT));
+        // the descriptor goes into the stage with plain stores; the arrive below releases them
+        // to every thread that acquires the barrier phase
+        *desc_s(s) = t;
+        mbar_arrive_expect_tx(&full_bar[s], bytes + sp.off_bytes + EPI::kStage * sp.in_bytes);
+        if (sp.cnt) bulk_g2s(idx_s(s), P.indices + sp.a0, sp.cnt * 4u, &full_bar[s], pol_stream);
+        if (WEIGHTED && sp.cnt)
+          bulk_g2s(w_s(s), weights + sp.a0, sp.cnt * static_cast<uint32_t>(sizeof(RT)), &full_bar[s],
                    pol_stream);
-        if (off_bytes) bulk_g2s(off_s(s), offsets + r0, off_bytes, &full_bar[s], pol_stream);
-        if (in_bytes) {
+        if (sp.off_bytes) bulk_g2s(off_s(s), offsets + sp.r0, sp.off_bytes, &full_bar[s], pol_stream);
+        if (sp.in_bytes) {
 #pragma unroll
           for (int k = 0; k < EPI::kStage; ++k)
-            bulk_g2s(in_s(s, k), epi.stage_src(k) + q0, in_bytes, &full_bar[s], pol_keep);
+            bulk_g2s(in_s(s, k), epi.stage_src(k) + sp.q0, sp.in_bytes, &full_bar[s], pol_keep);
         }
+        t = tn;
       }
+#ifdef B200_PROFILE_ROLES
+      b200_role_clocks[blockIdx.x][5] = prof_a;
+      b200_role_clocks[blockIdx.x][6] = my_n;
+#endif
     }
   } else if (warp < kGatherWarps) {
     // ================= gather warps =================
+#ifdef B200_EXP_NOGATHER  // experiment: what the kernel costs without the global gathers
+    auto gather1 = [&](int id) -> RT { return (id < hub_n) ? hub[id] : RT(1); };
+#else
     auto gather1 = [&](int id) -> RT { return (id < hub_n) ? hub[id] : ld_gather(x + id); };
+#endif
+    // Rolling software pipeline: a lane issues the four gathers of its next quad (possibly of
+    // the NEXT tile) before it retires the previous quad, so the L1TEX queue never drains at a
+    // tile boundary.  A pending quad carries the stage it belongs to; the warp arrives on that
+    // stage's `ready` barrier when it retires the tile's last quad.
+    constexpr int kStep = kGatherThreads * 4;
+    constexpr int kIter = (S::cap + kStep - 1) / kStep;
+    constexpr unsigned kActive = 1u, kLast = 2u, kChunk = 4u, kExists = 8u;
+    RT pv0 = RT(0), pv1 = RT(0), pv2 = RT(0), pv3 = RT(0);
+    int p_i = 0, p_s = 0;
+    unsigned p_flags = 0;
+    double part = 0.0;
+    auto retire = [&]() {
+      if (!(p_flags & kExists)) return;
+      const int s = p_s;
+      if (p_flags & kActive) {
+        RT v0 = pv0, v1 = pv1, v2 = pv2, v3 = pv3;
+        if (WEIGHTED) {
+          const RT* ws = w_s(s);
+          v0 *= ws[p_i]; v1 *= ws[p_i + 1]; v2 *= ws[p_i + 2]; v3 *= ws[p_i + 3];
+        }
+        if (p_flags & kChunk) {
+          // chunk of a long row: block-wide reduction, no shared-memory round trip
+          const tile_t tp = *desc_s(s);
+          const int lead  = static_cast<int>(tp.edge_first & 3);
+          const int hi    = lead + tp.num_edges;
+          RT sum4 = RT(0);
+          if (p_i >= lead && p_i < hi) sum4 += v0;
+          if (p_i + 1 >= lead && p_i + 1 < hi) sum4 += v1;
+          if (p_i + 2 >= lead && p_i + 2 < hi) sum4 += v2;
+          if (p_i + 3 >= lead && p_i + 3 < hi) sum4 += v3;
+          part += static_cast<double>(sum4);
+        } else {
+          RT* ps = prod_s(s) + p_i;
+          if constexpr (sizeof(RT) == 4) {
+            *reinterpret_cast<float4*>(ps) = make_float4(v0, v1, v2, v3);
+          } else {
+            *reinterpret_cast<double2*>(ps)     = make_double2(v0, v1);
+            *reinterpret_cast<double2*>(ps + 2) = make_double2(v2, v3);
+          }
+        }
+      }
+      if (p_flags & kLast) {
+        if (p_flags & kChunk) {
+          double tot = warp_sum(part);
+          if (lane == 0) warp_part[s][warp] = tot;
+          part = 0.0;
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&ready_bar[s]);
+      }
+      p_flags = 0;
+    };
     for (int64_t j = 0; j < my_n; ++j) {
-      const tile_t t    = P.tiles[blockIdx.x + j * stride];
       const int s       = static_cast<int>(j % STAGES);
       const uint32_t ph = static_cast<uint32_t>((j / STAGES) & 1);
+      {
+        B200_CLK(w0);
+        mbar_wait(&full_bar[s], ph);
+        B200_ACC(prof_a, w0);
+      }
+      const tile_t t    = *desc_s(s);
       const int lead    = static_cast<int>(t.edge_first & 3);
       const int cnt     = (lead + t.num_edges + 3) & ~3;
-      mbar_wait(&full_bar[s], ph);
       const int32_t* is = idx_s(s);
-      const RT* ws      = w_s(s);
-      RT* ps            = prod_s(s);
-      if (t.kind == 0) {
-        // up to 3 x 4 gathers per thread in flight before the first product is stored
-        constexpr int kStep = kGatherThreads * 4;
-        constexpr int kIter = (S::cap + kStep - 1) / kStep;
-        int4 id[kIter];
-        RT v[kIter][4];
+      const unsigned tile_flags = kExists | (t.kind != 0 ? kChunk : 0u);
 #pragma unroll
-        for (int u = 0; u < kIter; ++u) {
-          const int i = tid * 4 + u * kStep;
-          if (i < cnt) id[u] = *reinterpret_cast<const int4*>(is + i);
+      for (int u = 0; u < kIter; ++u) {
+        const int i    = tid * 4 + u * kStep;
+        const bool act = i < cnt;
+        RT n0 = RT(0), n1 = RT(0), n2 = RT(0), n3 = RT(0);
+        if (act) {
+          const int4 id = *reinterpret_cast<const int4*>(is + i);
+          n0 = gather1(id.x); n1 = gather1(id.y); n2 = gather1(id.z); n3 = gather1(id.w);
         }
-#pragma unroll
-        for (int u = 0; u < kIter; ++u) {
-          const int i = tid * 4 + u * kStep;
-          if (i < cnt) {
-            v[u][0] = gather1(id[u].x); v[u][1] = gather1(id[u].y);
-            v[u][2] = gather1(id[u].z); v[u][3] = gather1(id[u].w);
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < kIter; ++u) {
-          const int i = tid * 4 + u * kStep;
-          if (i < cnt) {
-            if (WEIGHTED) {
-              v[u][0] *= ws[i]; v[u][1] *= ws[i + 1]; v[u][2] *= ws[i + 2]; v[u][3] *= ws[i + 3];
-            }
-            ps[i] = v[u][0]; ps[i + 1] = v[u][1]; ps[i + 2] = v[u][2]; ps[i + 3] = v[u][3];
-          }
-        }
-      } else {
-        // chunk of a long row: block-wide reduction, no shared-memory round trip
-        double part  = 0.0;
-        const int hi = lead + t.num_edges;
-        for (int i = tid * 4; i < cnt; i += kGatherThreads * 4) {
-          int4 id = *reinterpret_cast<const int4*>(is + i);
-          RT v0 = gather1(id.x), v1 = gather1(id.y), v2 = gather1(id.z), v3 = gather1(id.w);
-          if (WEIGHTED) {
-            v0 *= ws[i]; v1 *= ws[i + 1]; v2 *= ws[i + 2]; v3 *= ws[i + 3];
-          }
-          RT sum4 = RT(0);
-          if (i >= lead && i < hi) sum4 += v0;
-          if (i + 1 >= lead && i + 1 < hi) sum4 += v1;
-          if (i + 2 >= lead && i + 2 < hi) sum4 += v2;
-          if (i + 3 >= lead && i + 3 < hi) sum4 += v3;
-          part += static_cast<double>(sum4);
-        }
-        part = warp_sum(part);
-        if (lane == 0) warp_part[s][warp] = part;
+        retire();
+        pv0 = n0; pv1 = n1; pv2 = n2; pv3 = n3;
+        p_i = i; p_s = s;
+        p_flags = tile_flags | (act ? kActive : 0u) | (u == kIter - 1 ? kLast : 0u);
       }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&ready_bar[s]);
     }
+    retire();
     // rows without edges: epilogue only (per_v...cuh:553-559 fills them with init)
+    B200_CLK(z0);
     {
       const int64_t step = static_cast<int64_t>(gridDim.x) * kGatherThreads;
       int64_t r = P.zero_first + static_cast<int64_t>(blockIdx.x) * kGatherThreads + tid;
@@ -265,19 +342,38 @@ __global__ void __launch_bounds__(kPullThreads, 1)
       }
       for (; r < P.num_rows; r += step) epi(r, RT(0), acc);
     }
+#ifdef B200_PROFILE_ROLES
+    B200_ACC(prof_b, z0);
+    if (tid == 0) {
+      b200_role_clocks[blockIdx.x][1] = prof_a;
+      b200_role_clocks[blockIdx.x][2] = prof_b;
+    }
+#endif
   } else {
     // ================= reduce warps =================
     const int rtid  = tid - kGatherThreads;
     const int rwarp = warp - kGatherWarps;
     for (int64_t j = 0; j < my_n; ++j) {
-      const tile_t t    = P.tiles[blockIdx.x + j * stride];
       const int s       = static_cast<int>(j % STAGES);
       const uint32_t ph = static_cast<uint32_t>((j / STAGES) & 1);
+      {
+        B200_CLK(w0);
+        mbar_wait(&full_bar[s], ph);   // descriptor + offsets landed (TMA)
+        B200_ACC(prof_a, w0);
+      }
+      const tile_t t    = *desc_s(s);
       const int lead    = static_cast<int>(t.edge_first & 3);
-      mbar_wait(&full_bar[s], ph);   // offsets landed (TMA)
-      mbar_wait(&ready_bar[s], ph);  // products written (gather warps)
+      {
+        B200_CLK(w1);
+        mbar_wait(&ready_bar[s], ph);  // products written (gather warps)
+        B200_ACC(prof_b, w1);
+      }
+#ifdef B200_EXP_NOREDUCE  // experiment: what the kernel costs without the row reductions
+      if (false) {
+#else
       if (t.kind == 0) {
-        const RT* ps      = prod_s(s);
+#endif
+        RT* ps            = prod_s(s);
         constexpr int per16 = 16 / sizeof(ET);
         constexpr int q16   = 16 / sizeof(RT);
         const ET* offp      = off_s(s) + (t.row_first & (per16 - 1));
@@ -286,28 +382,52 @@ __global__ void __launch_bounds__(kPullThreads, 1)
         const int64_t a0 = t.edge_first - lead;
         const int nrows  = t.num_rows;
         const int avg    = t.num_edges / (nrows > 0 ? nrows : 1);
-        // G lanes per row; the rounds of a group loop are uniform across the warp so that the
-        // shuffles always run with a full mask
+        // Step 1: row sums with G lanes per row, kU rows of a lane group in flight at once (the
+        // reduction is a chain of dependent shared-memory loads and shuffles: without the
+        // interleave it was latency-bound at ~2500 clocks per tile).  The sum of a non-empty
+        // row is left in the row's own first product slot.
         auto reduce_rows = [&](auto G_) {
           constexpr int G      = decltype(G_)::value;
           constexpr int groups = kReduceThreads / G;
+          constexpr int kU     = 4;
           const int gid = rtid / G, l = rtid % G;
           const int rounds = (nrows + groups - 1) / groups;
-          for (int k = 0; k < rounds; ++k) {
-            const int r    = k * groups + gid;
-            const bool act = r < nrows;
-            int b = 0, e = 0;
-            typename EPI::pre_t pre{};
-            if (act) {
-              b = static_cast<int>(static_cast<int64_t>(offp[r]) - a0);
-              e = static_cast<int>(static_cast<int64_t>(offp[r + 1]) - a0);
-              if (l == 0) pre = epi.from_staged(in0, in1, r, static_cast<int64_t>(t.row_first) + r);
-            }
-            RT sum = RT(0);
-            for (int i = b + l; i < e; i += G) sum += ps[i];
+          for (int k0 = 0; k0 < rounds; k0 += kU) {
+            int b[kU], e[kU], i[kU];
+            RT sum[kU];
 #pragma unroll
-            for (int o = G / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o, G);
-            if (act && l == 0) epi.finish(static_cast<int64_t>(t.row_first) + r, sum, pre, acc);
+            for (int u = 0; u < kU; ++u) {
+              const int r = (k0 + u) * groups + gid;
+              b[u] = 0; e[u] = 0;
+              if (r < nrows) {
+                b[u] = static_cast<int>(static_cast<int64_t>(offp[r]) - a0);
+                e[u] = static_cast<int>(static_cast<int64_t>(offp[r + 1]) - a0);
+              }
+              i[u]   = b[u] + l;
+              sum[u] = RT(0);
+            }
+            bool more = true;
+            while (more) {
+              more = false;
+#pragma unroll
+              for (int u = 0; u < kU; ++u) {
+                if (i[u] < e[u]) {
+                  sum[u] += ps[i[u]];
+                  i[u] += G;
+                  more = more || (i[u] < e[u]);
+                }
+              }
+            }
+#pragma unroll
+            for (int o = G / 2; o > 0; o >>= 1) {
+#pragma unroll
+              for (int u = 0; u < kU; ++u) sum[u] += __shfl_xor_sync(0xffffffffu, sum[u], o, G);
+            }
+            if (l == 0) {
+#pragma unroll
+              for (int u = 0; u < kU; ++u)
+                if (b[u] < e[u]) ps[b[u]] = sum[u];
+            }
           }
         };
         if (avg < 3) reduce_rows(std::integral_constant<int, 1>{});
@@ -316,6 +436,15 @@ __global__ void __launch_bounds__(kPullThreads, 1)
         else if (avg < 24) reduce_rows(std::integral_constant<int, 8>{});
         else if (avg < 48) reduce_rows(std::integral_constant<int, 16>{});
         else reduce_rows(std::integral_constant<int, 32>{});
+        // Step 2: the epilogue, one thread per row: independent iterations, coalesced stores
+        named_bar_sync(1, kReduceThreads);
+        for (int r = rtid; r < nrows; r += kReduceThreads) {
+          const int b = static_cast<int>(static_cast<int64_t>(offp[r]) - a0);
+          const int e = static_cast<int>(static_cast<int64_t>(offp[r + 1]) - a0);
+          const RT sum = (b < e) ? ps[b] : RT(0);
+          const int64_t row = static_cast<int64_t>(t.row_first) + r;
+          epi.finish(row, sum, epi.from_staged(in0, in1, r, row), acc);
+        }
       } else if (rwarp == 0) {
         double v = (lane < kGatherWarps) ? warp_part[s][lane] : 0.0;
         v        = warp_sum(v);
@@ -324,8 +453,18 @@ __global__ void __launch_bounds__(kPullThreads, 1)
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty_bar[s]);
     }
+#ifdef B200_PROFILE_ROLES
+    if (tid == kGatherThreads) {
+      b200_role_clocks[blockIdx.x][3] = prof_a;
+      b200_role_clocks[blockIdx.x][4] = prof_b;
+    }
+#endif
   }
 
+#ifdef B200_PROFILE_ROLES
+  __syncthreads();
+  if (tid == 0) b200_role_clocks[blockIdx.x][0] = clock64() - prof_t0;
+#endif
   // per-CTA partial sums of the epilogue scalars (fixed order: deterministic)
   if (P.cta_partials) {
     double a = warp_sum(acc.a), b = warp_sum(acc.b);

@@ -32,3 +32,17 @@ for r in range(a.reps):
     ms = st.elapsed_ms / a.iters
     print(f"  rep{r}: {ms:.4f} ms/iter  {ne/ms/1e6:.1f} GTEPS  algorithmic {bytes_iter/ms/1e6:.1f} GB/s "
           f"({bytes_iter/ms/1e6/6539.5*100:.1f}% of measured 6539.5)", flush=True)
+
+# tuning builds compiled with -DB200_PROFILE_ROLES export per-CTA role clocks of the last launch
+import ctypes
+from cugraph_forked_b200 import _lib
+if hasattr(_lib.lib(), "b200_debug_role_clocks"):
+    import numpy as np
+    buf = (ctypes.c_ulonglong * (256 * 8))()
+    _lib.lib().b200_debug_role_clocks(buf)
+    a = np.frombuffer(buf, dtype=np.uint64).reshape(256, 8)[:148].astype(np.float64)
+    names = ["kernel", "gather wait full", "gather zero rows", "reduce wait full",
+             "reduce wait ready", "producer wait empty", "tiles", "-"]
+    for k, nme in enumerate(names[:7]):
+        print(f"  role clocks {nme:22s} mean {a[:, k].mean():12.0f}  min {a[:, k].min():12.0f}  "
+              f"max {a[:, k].max():12.0f}")
