@@ -1,6 +1,9 @@
 // extern "C" surface of libcugraph_b200.so (include/b200_cugraph.h): argument checks, exception
 // -> error-code translation (what cpp/src/c_api/utils.hpp:25-56 `run_algorithm` does for the
 // reference) and the handle object.
+#include <cstdlib>
+#include <cstring>
+
 #include "centrality.cuh"
 
 namespace b200 {
@@ -35,6 +38,13 @@ static void fill_device_info(b200_handle* h)
   h->persisting_l2_max = static_cast<size_t>(prop.persistingL2CacheMaxSize);
   B200_EXPECTS(prop.major >= 10, kUnknownError,
                "libcugraph_b200 is built for sm_100a only: no Blackwell GPU on this device.");
+  // keep freed blocks in the default pool (dbuf allocates from it, common.cuh); the
+  // B200_POOL_RELEASE_MB environment variable caps what is kept
+  cudaMemPool_t pool{};
+  CUDA_TRY(cudaDeviceGetDefaultMemPool(&pool, h->device));
+  unsigned long long keep = ~0ull;
+  if (const char* v = std::getenv("B200_POOL_RELEASE_MB")) keep = std::strtoull(v, nullptr, 10) << 20;
+  CUDA_TRY(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
 }
 }  // namespace b200
 

@@ -69,23 +69,28 @@ void set_last_error(const char* msg);
     }                                                                                      \
   } while (0)
 
-// Owning device buffer (the role rmm::device_uvector plays in the reference). Allocation is
-// stream-ordered on the handle's stream; `pad` extra bytes are zero-filled so that 16-byte
-// bulk copies may run past the logical end.
+// Owning device buffer (the role rmm::device_uvector plays in the reference).  Allocation and
+// release are stream-ordered (cudaMallocAsync / cudaFreeAsync on the handle's stream) out of
+// the device's default memory pool, whose release threshold the handle raises so that freed
+// blocks stay cached - the role of the rmm pool resource: a graph build or a driver call then
+// costs no driver-level cudaMalloc / cudaFree (measured: 95 -> 675 ms build time drift at
+// scale 24 without the pool).  `pad` extra elements are zero-filled so that 16-byte bulk
+// copies may run past the logical end.
 template <typename T>
 struct dbuf {
   T* p{nullptr};
   size_t n{0};
+  cudaStream_t st{nullptr};
   dbuf() = default;
   dbuf(size_t count, cudaStream_t s, size_t pad_elems = 0) { alloc(count, s, pad_elems); }
   dbuf(dbuf const&)            = delete;
   dbuf& operator=(dbuf const&) = delete;
-  dbuf(dbuf&& o) noexcept : p(o.p), n(o.n) { o.p = nullptr; o.n = 0; }
+  dbuf(dbuf&& o) noexcept : p(o.p), n(o.n), st(o.st) { o.p = nullptr; o.n = 0; }
   dbuf& operator=(dbuf&& o) noexcept
   {
     if (this != &o) {
       release();
-      p = o.p; n = o.n; o.p = nullptr; o.n = 0;
+      p = o.p; n = o.n; st = o.st; o.p = nullptr; o.n = 0;
     }
     return *this;
   }
@@ -94,10 +99,11 @@ struct dbuf {
   {
     release();
     n            = count;
+    st           = s;
     size_t bytes = (count + pad_elems) * sizeof(T);
     if (bytes == 0) bytes = sizeof(T);
     bytes = (bytes + 255) & ~size_t{255};
-    CUDA_TRY(cudaMalloc(reinterpret_cast<void**>(&p), bytes));
+    CUDA_TRY(cudaMallocAsync(reinterpret_cast<void**>(&p), bytes, s));
     if (pad_elems) {
       CUDA_TRY(cudaMemsetAsync(reinterpret_cast<char*>(p) + count * sizeof(T), 0,
                                bytes - count * sizeof(T), s));
@@ -105,7 +111,13 @@ struct dbuf {
   }
   void release()
   {
-    if (p) cudaFree(p);
+    if (p) {
+      // the stream may be gone when a graph outlives its handle: fall back to the blocking call
+      if (cudaFreeAsync(p, st) != cudaSuccess) {
+        cudaGetLastError();
+        cudaFree(p);
+      }
+    }
     p = nullptr; n = 0;
   }
   T* data() const { return p; }
