@@ -200,6 +200,11 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
   if (tiled) {
     build_schedule(h, *ep, T, rowcap);
     main_ctas = h->sm_count;  // one persistent warp-specialised CTA per SM
+    // A CTA of this kernel takes the whole register file of its SM, so NCCL's kernels cannot
+    // share an SM with it.  On a multi-GPU grid the per-partition reductions run on a second
+    // stream while the next partition's kernel executes: leave them a few SMs.
+    if (g->multi_gpu && h->size > 1)
+      main_ctas = std::max(1, main_ctas - std::max(0, env_int("B200_MG_RESERVED_SMS", 16)));
     if (ep->num_tiles < main_ctas) main_ctas = static_cast<int>(std::max<int64_t>(ep->num_tiles, 1));
     // tail kernel: 8 lanes per long row, 32 rows per 256-thread block
     int64_t want_tail = div_up(std::max<int64_t>(ep->num_long_rows, 1), 32);
@@ -270,7 +275,20 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
                                     static_cast<int>(SM::total(SM::max_hub))));
       configured = true;
     }
-    P.hub_entries = hub;
+    // split the cache between the pieces of the minor range (one piece on a single GPU)
+    std::vector<int64_t> pieces = ep->minor_piece_offsets;
+    if (pieces.size() < 2 || pieces.size() - 1 > kMaxHubPieces) pieces = {0, ep->num_minors};
+    const int np  = static_cast<int>(pieces.size()) - 1;
+    int total     = 0;
+    P.hub_pieces  = np;
+    for (int k = 0; k < kMaxHubPieces; ++k) { P.hub_piece_start[k] = 0; P.hub_piece_len[k] = 0; }
+    for (int k = 0; k < np; ++k) {
+      int64_t len = std::min<int64_t>((hub / np) & ~31, pieces[k + 1] - pieces[k]);
+      P.hub_piece_start[k] = static_cast<int32_t>(pieces[k]);
+      P.hub_piece_len[k]   = static_cast<int32_t>(len);
+      total += static_cast<int>(len);
+    }
+    P.hub_entries = total;
     kern<<<main_ctas, kPullThreads, SM::total(hub), s>>>(P, epi);
   };
   auto go = [&](auto et, auto wtag) {

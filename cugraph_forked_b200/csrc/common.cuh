@@ -192,6 +192,10 @@ struct edge_partition {
   bool generic_schedule{false};
   dbuf<int32_t> long_row_ids;     // [n_long] (generic schedule only; else rows [0, n_long))
   int64_t zero_first{0};          // rows [zero_first, num_rows) have no edges
+  // the minor range is the concatenation of R vertex partitions, each in descending degree
+  // order: offsets of those pieces inside the range ({0, num_minors} on a single GPU).  The
+  // kernel's shared-memory hub cache takes the head of every piece.
+  std::vector<int64_t> minor_piece_offsets;
 };
 
 }  // namespace b200

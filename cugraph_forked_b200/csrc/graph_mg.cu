@@ -546,6 +546,10 @@ static void create_mg_t(b200_handle* h, const VT* src, const VT* dst, const void
     ep.major_first = vpo[R * i + row_rank];
     ep.minor_first = minor_first;
     ep.num_minors  = n_minor;
+    ep.minor_piece_offsets.assign(1, 0);
+    for (int j = 0; j < R; ++j)
+      ep.minor_piece_offsets.push_back(ep.minor_piece_offsets.back() +
+                                       static_cast<int64_t>(minor_counts[j]));
     ep.offsets64   = n >= static_cast<size_t>(0x7fffffff);
     ep.indices.alloc(n, s, 16);
     if (weights) ep.weights.alloc(n * wsize, s, 32);

@@ -9,7 +9,9 @@
 //      allreduced over all ranks; the stop test stays on the device, every rank sees the same
 //      scalars and therefore stops at the same iteration
 // Every rank calls these functions collectively with the same arguments.
+#include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 
 #include "centrality.cuh"
@@ -278,6 +280,36 @@ struct mg_engine {
   // device-time of the partitions' kernels on the main stream
   std::vector<cudaEvent_t> ev_time;
   int timed{0};
+  // B200_MG_TRACE=1: per-phase device times of the first iterations, printed by rank 0
+  bool trace{false};
+  std::vector<cudaEvent_t> ev_trace;  // 5 per iteration: start, gathered, kernels, reduced, end
+  void mark(int k)
+  {
+    if (!trace || ev_trace.size() >= 5 * 64 + 5) return;
+    if (k == 0 && ev_trace.size() % 5 != 0) return;
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    cudaEventRecord(e, h->stream);
+    ev_trace.push_back(e);
+  }
+  void print_trace()
+  {
+    if (!trace || h->rank != 0) return;
+    size_t iters = ev_trace.size() / 5;
+    if (iters == 0) return;
+    double acc[4] = {0, 0, 0, 0};
+    for (size_t i = 0; i < iters; ++i)
+      for (int k = 0; k < 4; ++k) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, ev_trace[5 * i + k], ev_trace[5 * i + k + 1]);
+        acc[k] += ms;
+      }
+    fprintf(stderr,
+            "[b200 mg trace] %zu iterations: allgather %.1f us, partition kernels %.1f us, "
+            "reduce tail %.1f us, vertex pass + allreduce %.1f us\n",
+            iters, 1e3 * acc[0] / iters, 1e3 * acc[1] / iters, 1e3 * acc[2] / iters,
+            1e3 * acc[3] / iters);
+  }
 
   mg_engine(b200_handle* h_, b200_graph* g_) : h(h_), g(g_)
   {
@@ -305,20 +337,26 @@ struct mg_engine {
     ev_part.resize(C);
     for (auto& e : ev_part) CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     CUDA_TRY(cudaEventCreateWithFlags(&ev_red, cudaEventDisableTiming));
+    trace = env_int("B200_MG_TRACE", 0) != 0;
   }
   ~mg_engine()
   {
+    for (auto e : ev_trace) cudaEventDestroy(e);
     for (auto p : parts) partition_spmv_free(p);
     for (auto e : ev_part) cudaEventDestroy(e);
     for (auto e : ev_time) cudaEventDestroy(e);
     if (ev_red) cudaEventDestroy(ev_red);
+    if (ev_fold) cudaEventDestroy(ev_fold);
+    if (ev_commit) cudaEventDestroy(ev_commit);
   }
 
   // sum[local v] = sum over all edges into v of x[src], x given for the local vertices
   void spmv(const RT* x_local)
   {
     cudaStream_t s = h->stream;
+    mark(0);
     allgatherv(s, h->row, R, h->row_rank, x_local, x_minor.data(), row_counts, sizeof(RT));
+    mark(1);
     const bool time_it = timed < 256;
     if (time_it) {
       cudaEvent_t a, b;
@@ -342,29 +380,59 @@ struct mg_engine {
       CUDA_TRY(cudaEventRecord(ev_time[2 * timed + 1], s));
       ++timed;
     }
+    mark(2);
     if (C > 1) {
       CUDA_TRY(cudaEventRecord(ev_red, h->comm_stream));
       CUDA_TRY(cudaStreamWaitEvent(s, ev_red, 0));
     }
+    mark(3);
   }
   const RT* result() const { return C == 1 ? partial[0].data() : sum.data(); }
 
-  // scal = allreduce(fold(partials)); then commit into the state
-  void reduce_scalars(double threshold, int64_t iteration, bool check, int which)
+  // scal = allreduce(fold(partials)); then commit into the state.  With `deferred` the
+  // allreduce and the commit run on the second stream and the caller joins them with
+  // join_scalars() right before the next consumer of the state (the next vertex pass): the
+  // ~100 us small-message latency then hides behind the next iteration's exchange and kernels.
+  cudaEvent_t ev_fold{}, ev_commit{};
+  bool pending_join{false};
+  void reduce_scalars(double threshold, int64_t iteration, bool check, int which,
+                      bool deferred = false)
   {
     cudaStream_t s = h->stream;
     mg_fold_kernel<<<1, 256, 0, s>>>(partials.data(), static_cast<int>(vg), state.data(), scal.data());
     CUDA_TRY(cudaGetLastError());
+    cudaStream_t cs = s;
+    if (deferred && h->size > 1) {
+      if (!ev_fold) {
+        CUDA_TRY(cudaEventCreateWithFlags(&ev_fold, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&ev_commit, cudaEventDisableTiming));
+      }
+      cs = h->comm_stream;
+      CUDA_TRY(cudaEventRecord(ev_fold, s));
+      CUDA_TRY(cudaStreamWaitEvent(cs, ev_fold, 0));
+    }
     if (h->size > 1)
-      NCCL_TRY(ncclAllReduce(scal.data(), scal.data(), 2, ncclDouble, ncclSum, h->world, s));
-    mg_commit_kernel<<<1, 1, 0, s>>>(scal.data(), state.data(), threshold, iteration, check ? 1 : 0,
-                                     which);
+      NCCL_TRY(ncclAllReduce(scal.data(), scal.data(), 2, ncclDouble, ncclSum, h->world, cs));
+    mg_commit_kernel<<<1, 1, 0, cs>>>(scal.data(), state.data(), threshold, iteration, check ? 1 : 0,
+                                      which);
     CUDA_TRY(cudaGetLastError());
+    if (cs != s) {
+      CUDA_TRY(cudaEventRecord(ev_commit, cs));
+      pending_join = true;
+    }
     launches += 2;
+    if (iteration > 0) mark(4);
+  }
+  void join_scalars()
+  {
+    if (!pending_join) return;
+    CUDA_TRY(cudaStreamWaitEvent(h->stream, ev_commit, 0));
+    pending_join = false;
   }
 
   iter_state read_state()
   {
+    join_scalars();
     iter_state hs;
     CUDA_TRY(cudaMemcpyAsync(&hs, state.data(), sizeof hs, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
@@ -373,6 +441,7 @@ struct mg_engine {
 
   void fill_stats(b200_centrality_stats_t* st, iter_state const& hs, double ms)
   {
+    print_trace();
     if (!st) return;
     st->iterations   = hs.iterations;
     st->converged    = hs.converged;
@@ -519,22 +588,29 @@ static void pagerank_mg_t(b200_handle* h, b200_graph* g, const b200_pagerank_par
 
   const int check_every = std::max(1, env_int("B200_CHECK_EVERY", 8));
   scoped_timer timer(s);
+  const auto host_t0 = std::chrono::steady_clock::now();
   iter_state hs{};
   for (int64_t it = 0; it < cap; ++it) {
     E.spmv(x.data());
+    E.join_scalars();  // the dangling mass and the stop flag of the previous iteration
     mg_pagerank_update_kernel<RT><<<E.vg, kVT, 0, s>>>(
       pr.data(), E.result(), scale.data(), personalized ? pers.data() : nullptr, x.data(), n,
       E.state.data(), alpha, static_cast<RT>(1.0 - p->alpha), static_cast<RT>(g->num_vertices),
       E.partials.data());
     CUDA_TRY(cudaGetLastError());
     ++E.launches;
-    E.reduce_scalars(static_cast<double>(epsilon), it + 1, !fixed, 3);
+    E.reduce_scalars(static_cast<double>(epsilon), it + 1, !fixed, 3, true);
     if (!fixed && ((it + 1) % check_every == 0)) {
       hs = E.read_state();
       if (hs.done) break;
     }
   }
+  const double host_ms =
+    std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - host_t0).count();
+  E.join_scalars();
   double ms = timer.stop();
+  if (E.trace && h->rank == 0)
+    fprintf(stderr, "[b200 mg trace] host enqueue %.3f ms, device %.3f ms for the loop\n", host_ms, ms);
   hs        = E.read_state();
   E.fill_stats(stats, hs, ms);
   if (n) CUDA_TRY(cudaMemcpyAsync(pr_user, pr.data(), n * sizeof(RT), cudaMemcpyDeviceToDevice, s));

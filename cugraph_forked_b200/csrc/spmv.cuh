@@ -50,7 +50,12 @@ struct pull_params {
   double* chunk_partials;  // [num_chunks]
   double* cta_partials;    // [2 (a,b)][slots]  written at [blockIdx.x]
   int32_t slots;
-  int32_t hub_entries;     // leading entries of x cached in shared memory
+  int32_t hub_entries;     // entries of x cached in shared memory, all pieces together
+  // the cached entries are the heads of up to kMaxHubPieces pieces of x (one on a single GPU;
+  // one per row_comm peer on a 2D grid, whose minor range concatenates R degree-sorted ranges)
+  int32_t hub_pieces;
+  int32_t hub_piece_start[4];  // first x index of piece k
+  int32_t hub_piece_len[4];    // cached entries of piece k (sum = hub_entries)
   const iter_state* state; // may be nullptr (raw spmv)
 };
 
@@ -66,6 +71,7 @@ __device__ unsigned long long b200_role_clocks[256][8];
 #define B200_ACC(acc, t0)
 #endif
 
+constexpr int kMaxHubPieces  = 4;
 constexpr int kLongRowDegree = 1024;  // = mid_degree_threshold, graph_view.hpp:255-263
 
 // tuning builds override the warp split (scripts/build_variant.sh); 31 worker warps in total
@@ -160,8 +166,16 @@ __global__ void __launch_bounds__(kPullThreads, 1)
     }
     fence_mbar_init();
   }
-  // hub cache: the highest-degree sources live at the front of x (degree-descending ids)
-  for (int i = tid; i < hub_n; i += kPullThreads) hub[i] = x[i];
+  // hub cache: the highest-degree sources live at the front of every piece of x
+  // (degree-descending ids)
+  {
+    int base = 0;
+    for (int k = 0; k < P.hub_pieces; ++k) {
+      const RT* xp = x + P.hub_piece_start[k];
+      for (int i = tid; i < P.hub_piece_len[k]; i += kPullThreads) hub[base + i] = xp[i];
+      base += P.hub_piece_len[k];
+    }
+  }
   epi.setup(P.state);
   __syncthreads();
 
@@ -241,10 +255,31 @@ __global__ void __launch_bounds__(kPullThreads, 1)
     }
   } else if (warp < kGatherWarps) {
     // ================= gather warps =================
+    const int hub0 = P.hub_piece_len[0];
+    const bool multi_piece = P.hub_pieces > 1;
+    auto hub_slot = [&](int id) -> int {
+      // slot of x[id] in the shared-memory cache, or -1
+      if (id < hub0) return id;
+      if (multi_piece) {
+        int base = hub0;
+#pragma unroll
+        for (int k = 1; k < kMaxHubPieces; ++k) {
+          if (k < P.hub_pieces) {
+            const unsigned d = static_cast<unsigned>(id - P.hub_piece_start[k]);
+            if (d < static_cast<unsigned>(P.hub_piece_len[k])) return base + static_cast<int>(d);
+            base += P.hub_piece_len[k];
+          }
+        }
+      }
+      return -1;
+    };
 #ifdef B200_EXP_NOGATHER  // experiment: what the kernel costs without the global gathers
-    auto gather1 = [&](int id) -> RT { return (id < hub_n) ? hub[id] : RT(1); };
+    auto gather1 = [&](int id) -> RT { const int sl = hub_slot(id); return sl >= 0 ? hub[sl] : RT(1); };
 #else
-    auto gather1 = [&](int id) -> RT { return (id < hub_n) ? hub[id] : ld_gather(x + id); };
+    auto gather1 = [&](int id) -> RT {
+      const int sl = hub_slot(id);
+      return sl >= 0 ? hub[sl] : ld_gather(x + id);
+    };
 #endif
     // Rolling software pipeline: a lane issues the four gathers of its next quad (possibly of
     // the NEXT tile) before it retires the previous quad, so the L1TEX queue never drains at a
