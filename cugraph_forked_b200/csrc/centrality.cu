@@ -203,8 +203,11 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
     // A CTA of this kernel takes the whole register file of its SM, so NCCL's kernels cannot
     // share an SM with it.  On a multi-GPU grid the per-partition reductions run on a second
     // stream while the next partition's kernel executes: leave them a few SMs.
-    if (g->multi_gpu && h->size > 1)
-      main_ctas = std::max(1, main_ctas - std::max(0, env_int("B200_MG_RESERVED_SMS", 16)));
+    if (g->multi_gpu && h->size > 1) {
+      // the fused rectangle overlaps only the 2-scalar allreduce of the previous iteration
+      const bool fused = !g->fused.empty() && ep == &g->fused[0];
+      main_ctas = std::max(1, main_ctas - std::max(0, env_int("B200_MG_RESERVED_SMS", fused ? 4 : 16)));
+    }
     if (ep->num_tiles < main_ctas) main_ctas = static_cast<int>(std::max<int64_t>(ep->num_tiles, 1));
     // tail kernel: 8 lanes per long row, 32 rows per 256-thread block
     int64_t want_tail = div_up(std::max<int64_t>(ep->num_long_rows, 1), 32);
@@ -910,9 +913,11 @@ partition_spmv* partition_spmv_create(b200_handle* h, b200_graph* g, int part, i
 {
   auto* p       = new partition_spmv();
   p->value_type = value_type;
+  // part < 0: the fused rectangle of a multi-GPU graph (all local partitions in one launch)
+  edge_partition* ep = part < 0 ? &g->fused.at(0) : &g->parts.at(part);
   try {
-    if (value_type == B200_FLOAT32) p->lf.init(h, g, &g->parts[part]);
-    else p->ld.init(h, g, &g->parts[part]);
+    if (value_type == B200_FLOAT32) p->lf.init(h, g, ep);
+    else p->ld.init(h, g, ep);
   } catch (...) {
     delete p;
     throw;

@@ -215,6 +215,11 @@ struct b200_graph {
   std::vector<std::vector<int64_t>> partition_segment_offsets;  // MG: one per edge partition
   b200::dbuf<char> renumber_map;  // vertex_type [local V]: internal -> external
   std::vector<b200::edge_partition> parts;  // SG: 1; MG: col_comm_size
+  // MG: the C local partitions again as ONE rectangle (rows = the concatenated major ranges,
+  // absolute edge offsets), which the drivers run as a single launch per iteration; the
+  // per-partition copies above are what the views and the parity tests read.
+  std::vector<b200::edge_partition> fused;      // 0 or 1 entries
+  std::vector<int64_t> fused_row_first;         // size C + 1: rows of partition i inside `fused`
   int64_t segment_offsets[8]{};
   int num_segments{0};
   // cached out-weight sums (double precision master copy, local vertices)

@@ -9,6 +9,8 @@
 // build sorts the gathered label arrays once and binary-searches them; where it compresses
 // each partition with atomics and a segmented sort, one stable radix sort of
 // (concatenated major row << 32 | minor offset) keys lays out all local partitions at once.
+#include <cstdlib>
+
 #include "graph_kernels.cuh"
 #include "mg_comm.cuh"
 
@@ -591,6 +593,53 @@ static void create_mg_t(b200_handle* h, const VT* src, const VT* dst, const void
     ep.generic_schedule = true;
     ep.seg[0] = 0; ep.seg[1] = seg[1]; ep.seg[2] = seg[2]; ep.seg[3] = seg[nseg - 2];
     ep.seg[4] = ep.num_rows;
+  }
+  // ---- 9. (opt-in, B200_MG_FUSED=1) the same edges once more as a single rectangle over the
+  //         concatenated major ranges: one launch per iteration instead of C; see mg.cu for
+  //         the measurement that keeps it off by default ----
+  g->fused.clear();
+  g->fused_row_first.assign(major_piece_first.begin(), major_piece_first.end());
+  const char* want_fused = std::getenv("B200_MG_FUSED");
+  if (C > 1 && want_fused && std::atoi(want_fused) != 0) {
+    g->fused.resize(1);
+    edge_partition& fp = g->fused[0];
+    fp.num_rows    = n_major;
+    fp.num_edges   = static_cast<int64_t>(ne);
+    fp.major_first = -1;  // not one global range
+    fp.minor_first = minor_first;
+    fp.num_minors  = n_minor;
+    fp.minor_piece_offsets = g->parts[0].minor_piece_offsets;
+    fp.offsets64   = ne >= static_cast<size_t>(0x7fffffff);
+    fp.indices.alloc(ne, s, 16);
+    if (weights) fp.weights.alloc(ne * wsize, s, 32);
+    if (ne) {
+      if (!weights)
+        finish_edges_kernel<float><<<grid_for(ne, 4), kThreads, 0, s>>>(ks, vs, ne, nullptr,
+                                                                      fp.indices.data(), nullptr);
+      else if (wsize == 4)
+        finish_edges_kernel<float><<<grid_for(ne, 4), kThreads, 0, s>>>(
+          ks, vs, ne, reinterpret_cast<const float*>(e_w.data()), fp.indices.data(),
+          reinterpret_cast<float*>(fp.weights.data()));
+      else
+        finish_edges_kernel<double><<<grid_for(ne, 4), kThreads, 0, s>>>(
+          ks, vs, ne, reinterpret_cast<const double*>(e_w.data()), fp.indices.data(),
+          reinterpret_cast<double*>(fp.weights.data()));
+      CUDA_TRY(cudaGetLastError());
+    }
+    const size_t nr = static_cast<size_t>(n_major);
+    if (fp.offsets64) {
+      fp.offsets.alloc((nr + 1) * 8, s, 64);
+      partition_offsets_kernel<int64_t><<<grid_for(nr + 1, 4), kThreads, 0, s>>>(
+        row_start.data(), 0, n_major, reinterpret_cast<int64_t*>(fp.offsets.data()));
+    } else {
+      fp.offsets.alloc((nr + 1) * 4, s, 64);
+      partition_offsets_kernel<int32_t><<<grid_for(nr + 1, 4), kThreads, 0, s>>>(
+        row_start.data(), 0, n_major, reinterpret_cast<int32_t*>(fp.offsets.data()));
+    }
+    CUDA_TRY(cudaGetLastError());
+    fp.has_segments     = true;
+    fp.generic_schedule = true;
+    fp.seg[4]           = n_major;
   }
   CUDA_TRY(cudaStreamSynchronize(s));
 

@@ -277,6 +277,7 @@ struct mg_engine {
   std::vector<cudaEvent_t> ev_part;
   cudaEvent_t ev_red{};
   int64_t launches{0};
+  bool fused{false};
   // device-time of the partitions' kernels on the main stream
   std::vector<cudaEvent_t> ev_time;
   int timed{0};
@@ -319,10 +320,23 @@ struct mg_engine {
     nloc           = static_cast<size_t>(g->local_last - g->local_first);
     n_minor        = static_cast<size_t>(g->parts[0].num_minors);
     int vt         = sizeof(RT) == 4 ? B200_FLOAT32 : B200_FLOAT64;
-    parts.assign(C, nullptr);
-    for (int i = 0; i < C; ++i) parts[i] = partition_spmv_create(h, g, i, vt);
-    partial.resize(C);
-    for (int i = 0; i < C; ++i) partial[i].alloc(static_cast<size_t>(g->parts[i].num_rows), s, 8);
+    // One launch over all local partitions (B200_MG_FUSED=1, also read at graph creation) was
+    // measured against the default of one launch per partition whose reduction overlaps the
+    // next kernel: at 8 GPUs / scale 24 the fused kernel is 17 % faster but its C reductions
+    // no longer overlap anything (118 vs 41 us), 545 vs 585 GTEPS overall - so it is opt-in.
+    fused = !g->fused.empty() && env_int("B200_MG_FUSED", 0) != 0;
+    if (fused) {
+      // one launch over all local partitions; partial sums of partition i are the rows
+      // [fused_row_first[i], fused_row_first[i + 1]) of one result buffer
+      parts.assign(1, partition_spmv_create(h, g, -1, vt));
+      partial.resize(1);
+      partial[0].alloc(static_cast<size_t>(g->fused[0].num_rows), s, 8);
+    } else {
+      parts.assign(C, nullptr);
+      for (int i = 0; i < C; ++i) parts[i] = partition_spmv_create(h, g, i, vt);
+      partial.resize(C);
+      for (int i = 0; i < C; ++i) partial[i].alloc(static_cast<size_t>(g->parts[i].num_rows), s, 8);
+    }
     x_minor.alloc(n_minor, s, 8);
     sum.alloc(nloc, s, 8);
     auto const& vpo = g->vertex_partition_offsets;
@@ -365,6 +379,25 @@ struct mg_engine {
       ev_time.push_back(a);
       ev_time.push_back(b);
       CUDA_TRY(cudaEventRecord(a, s));
+    }
+    if (fused) {
+      partition_spmv_run(parts[0], x_minor.data(), partial[0].data(), state.data());
+      if (time_it) {
+        CUDA_TRY(cudaEventRecord(ev_time[2 * timed + 1], s));
+        ++timed;
+      }
+      mark(2);
+      // every partition's partial sums go to the col_comm rank that owns those majors
+      NCCL_TRY(ncclGroupStart());
+      for (int i = 0; i < C; ++i) {
+        size_t cnt = static_cast<size_t>(g->parts[i].num_rows);
+        if (cnt)
+          NCCL_TRY(ncclReduce(partial[0].data() + g->fused_row_first[i], sum.data(), cnt,
+                              nccl_type<RT>::value, ncclSum, i, h->col, s));
+      }
+      NCCL_TRY(ncclGroupEnd());
+      mark(3);
+      return;
     }
     for (int i = 0; i < C; ++i) {
       partition_spmv_run(parts[i], x_minor.data(), partial[i].data(), state.data());
