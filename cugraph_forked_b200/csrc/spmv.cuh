@@ -276,6 +276,10 @@ __global__ void __launch_bounds__(kPullThreads, 1)
 #ifdef B200_EXP_NOGATHER  // experiment: what the kernel costs without the global gathers
     auto gather1 = [&](int id) -> RT { const int sl = hub_slot(id); return sl >= 0 ? hub[sl] : RT(1); };
 #else
+    // Tried and measured slower (profiles/r1_sweep_l1_hot.log, r1_notes.md): no-allocate loads
+    // for the cold tail of x (-15 %); the zero-row epilogues interleaved into the reduce warps
+    // instead of after the gather warps' tiles (-9 %: the reduce path is on the ring's
+    // critical path, the gather warps' tail is not).
     auto gather1 = [&](int id) -> RT {
       const int sl = hub_slot(id);
       return sl >= 0 ? hub[sl] : ld_gather(x + id);

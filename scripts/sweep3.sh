@@ -1,3 +1,4 @@
 mkdir -p gpurun_out
-(for c in 0 1 2 3 4 5; do for kb in 160 184; do echo "== CFG $c budget $kb"; B200_SMEM_BUDGET_KB=$kb B200_PULL_CFG=$c timeout 200 python scripts/gpu_perf.py --scale 24 --reps 2 | tail -1; done; done
-) 2>&1 | tee gpurun_out/sweep3.log | tail -70
+(echo "== base"; timeout 200 python scripts/gpu_perf.py --scale 24 --reps 2 | tail -1
+for v in hot64k hot256k hot1m prof; do echo "== $v"; B200_LIBRARY=$PWD/cugraph_forked_b200/variants/libcugraph_b200_$v.so timeout 200 python scripts/gpu_perf.py --scale 24 --reps 2 | tail -8 | grep -v "rep0\|^s24"; done
+) 2>&1 | tee gpurun_out/sweep4.log | tail -70
