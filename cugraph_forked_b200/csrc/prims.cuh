@@ -159,48 +159,108 @@ __global__ void __launch_bounds__(kSortThreads) radix_hist_kernel(const K* keys,
   hist[static_cast<size_t>(threadIdx.x) * nblocks + blockIdx.x] = h[threadIdx.x];
 }
 
+// One tile of kSortChunk elements per block.  The tile is first sorted by digit inside shared
+// memory (stable: rounds in order, warps in order, lanes ranked with match_any), then written
+// out so that consecutive threads store consecutive addresses of the same digit's run - the
+// direct register -> global scatter of the first version wrote one 8-byte key per 32-byte
+// sector and ran at ~12 % of its HBM roofline (profiles/r1b_ncu_pull_tiles_s24_f32.md).
+template <typename K, bool HAS_V>
+struct scatter_smem {
+  static constexpr size_t keys  = sizeof(K) * kSortChunk;
+  static constexpr size_t vals  = HAS_V ? sizeof(uint32_t) * kSortChunk : 0;
+  static constexpr size_t cnt   = sizeof(uint32_t) * (kSortThreads / 32) * 256;
+  static constexpr size_t small = sizeof(uint32_t) * 256 * 3;  // running, lstart, gbase
+  static constexpr size_t total = keys + vals + cnt + small;
+};
+
 template <typename K, bool HAS_V>
 __global__ void __launch_bounds__(kSortThreads) radix_scatter_kernel(
   const K* kin, K* kout, const uint32_t* vin, uint32_t* vout, const uint32_t* bases, size_t n,
   int shift, uint32_t nblocks)
 {
-  __shared__ uint32_t warp_cnt[kSortThreads / 32][256];
-  __shared__ uint32_t running[256];
+  extern __shared__ __align__(16) unsigned char sort_smem[];
+  using S = scatter_smem<K, HAS_V>;
+  K* skey            = reinterpret_cast<K*>(sort_smem);
+  uint32_t* sval     = reinterpret_cast<uint32_t*>(sort_smem + S::keys);
+  uint32_t* warp_cnt = reinterpret_cast<uint32_t*>(sort_smem + S::keys + S::vals);  // [8][256]
+  uint32_t* running  = warp_cnt + (kSortThreads / 32) * 256;  // per digit: elements so far
+  uint32_t* lstart   = running + 256;                         // per digit: start inside the tile
+  uint32_t* gbase    = lstart + 256;                          // per digit: start in the output
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  running[tid] = bases[static_cast<size_t>(tid) * nblocks + blockIdx.x];
-  size_t base  = static_cast<size_t>(blockIdx.x) * kSortChunk;
-  for (int r = 0; r < kSortRounds; ++r) {
-    if (base + static_cast<size_t>(r) * kSortThreads >= n) break;  // uniform
+  const size_t base = static_cast<size_t>(blockIdx.x) * kSortChunk;
+  running[tid] = 0;
+  gbase[tid]   = bases[static_cast<size_t>(tid) * nblocks + blockIdx.x];
+
+  K key[kSortRounds];
+  uint32_t val[kSortRounds];
+  uint16_t lpos[kSortRounds];
 #pragma unroll
-    for (int i = 0; i < kSortThreads / 32; ++i) warp_cnt[i][tid] = 0;
+  for (int r = 0; r < kSortRounds; ++r) {
+    const size_t idx = base + static_cast<size_t>(r) * kSortThreads + tid;
+    key[r] = idx < n ? kin[idx] : K(0);
+    val[r] = 0;
+    if (HAS_V && idx < n) val[r] = vin[idx];
+  }
+#pragma unroll
+  for (int r = 0; r < kSortRounds; ++r) {
+#pragma unroll
+    for (int i = 0; i < kSortThreads / 32; ++i) warp_cnt[i * 256 + tid] = 0;
     __syncthreads();
-    size_t idx  = base + static_cast<size_t>(r) * kSortThreads + tid;
-    bool valid  = idx < n;
-    K key       = valid ? kin[idx] : K(0);
-    uint32_t v  = 0;
-    if (HAS_V && valid) v = vin[idx];
-    int digit     = valid ? static_cast<int>((key >> shift) & 255) : 256;
-    unsigned mask = __match_any_sync(0xffffffffu, digit);
-    int rank      = __popc(mask & ((1u << lane) - 1u));
-    if (valid && rank == 0) warp_cnt[w][digit] = __popc(mask);
+    const bool valid    = base + static_cast<size_t>(r) * kSortThreads + tid < n;
+    const int digit     = valid ? static_cast<int>((key[r] >> shift) & 255) : 256;
+    const unsigned mask = __match_any_sync(0xffffffffu, digit);
+    const int rank      = __popc(mask & ((1u << lane) - 1u));
+    if (valid && rank == 0) warp_cnt[w * 256 + digit] = __popc(mask);
     __syncthreads();
     {
       uint32_t run = running[tid];
 #pragma unroll
       for (int i = 0; i < kSortThreads / 32; ++i) {
-        uint32_t c     = warp_cnt[i][tid];
-        warp_cnt[i][tid] = run;
+        const uint32_t c        = warp_cnt[i * 256 + tid];
+        warp_cnt[i * 256 + tid] = run;
         run += c;
       }
       running[tid] = run;
     }
     __syncthreads();
-    if (valid) {
-      uint32_t pos = warp_cnt[w][digit] + rank;
-      kout[pos]    = key;
-      if (HAS_V) vout[pos] = v;
-    }
+    lpos[r] = valid ? static_cast<uint16_t>(warp_cnt[w * 256 + digit] + rank) : uint16_t(0);
     __syncthreads();
+  }
+  // running[] is now the tile's histogram: exclusive scan over the 256 digits
+  {
+    const uint32_t c = running[tid];
+    uint32_t inc     = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += u;
+    }
+    if (lane == 31) warp_cnt[w] = inc;
+    __syncthreads();
+    uint32_t off = 0;
+#pragma unroll
+    for (int i = 0; i < kSortThreads / 32; ++i)
+      if (i < w) off += warp_cnt[i];
+    lstart[tid] = off + inc - c;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < kSortRounds; ++r) {
+    if (base + static_cast<size_t>(r) * kSortThreads + tid < n) {
+      const uint32_t p = lstart[(key[r] >> shift) & 255] + lpos[r];
+      skey[p]          = key[r];
+      if (HAS_V) sval[p] = val[r];
+    }
+  }
+  __syncthreads();
+  const uint32_t ntile =
+    static_cast<uint32_t>(n - base < static_cast<size_t>(kSortChunk) ? n - base : kSortChunk);
+  for (uint32_t j = tid; j < ntile; j += kSortThreads) {
+    const K k        = skey[j];
+    const uint32_t d = static_cast<uint32_t>((k >> shift) & 255);
+    const uint32_t g = gbase[d] + (j - lstart[d]);
+    kout[g]          = k;
+    if (HAS_V) vout[g] = sval[j];
   }
 }
 
@@ -225,13 +285,20 @@ int radix_sort(K* k0, K* k1, uint32_t* v0, uint32_t* v1, size_t n,
       CUDA_TRY(cudaGetLastError());
       exclusive_scan<uint32_t, uint32_t>(hist.data(), hist.data(),
                                          static_cast<size_t>(nblocks) * 256, s);
-      if (v0)
-        radix_scatter_kernel<K, true>
-          <<<nblocks, kSortThreads, 0, s>>>(kin, kout, vin, vout, hist.data(), n, shift, nblocks);
-      else
-        radix_scatter_kernel<K, false>
-          <<<nblocks, kSortThreads, 0, s>>>(kin, kout, nullptr, nullptr, hist.data(), n, shift,
-                                            nblocks);
+      if (v0) {
+        auto kern = radix_scatter_kernel<K, true>;
+        constexpr size_t smem = scatter_smem<K, true>::total;
+        CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      static_cast<int>(smem)));
+        kern<<<nblocks, kSortThreads, smem, s>>>(kin, kout, vin, vout, hist.data(), n, shift, nblocks);
+      } else {
+        auto kern = radix_scatter_kernel<K, false>;
+        constexpr size_t smem = scatter_smem<K, false>::total;
+        CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      static_cast<int>(smem)));
+        kern<<<nblocks, kSortThreads, smem, s>>>(kin, kout, nullptr, nullptr, hist.data(), n, shift,
+                                                 nblocks);
+      }
       CUDA_TRY(cudaGetLastError());
       cur ^= 1;
     }
