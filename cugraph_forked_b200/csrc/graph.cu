@@ -10,6 +10,8 @@
 // by ONE stable radix sort of (new_major << 32 | new_minor) keys, which yields the offsets
 // (from the already sorted degrees), the ascending neighbour lists and a deterministic weight
 // order at once.
+#include <cstdlib>
+
 #include "graph.cuh"
 #include "graph_kernels.cuh"
 
@@ -19,6 +21,44 @@ namespace b200 {
 // ------------------------------------------------------------------------------------------
 // schedule
 // ------------------------------------------------------------------------------------------
+// The tile list is built heavy-first: chunks of the hub rows (all gather, no row work), then row
+// tiles by descending degree, then runs of low-degree rows (little to gather, most row work).
+// CTA c walks positions c, c + G, c + 2G, ...; taking blocks of G tiles alternately from the
+// front and from the back of the list makes every CTA alternate gather-heavy and
+// reduce-heavy tiles, so its gather and reduce warps are busy at the same time instead of in
+// turn.  Any order is valid (chunk partials are addressed by tile.aux).
+static void interleave_tiles(b200_handle* h, edge_partition& ep)
+{
+  const char* env = std::getenv("B200_TILE_INTERLEAVE");
+  if (env && std::atoi(env) == 0) return;
+  cudaStream_t s  = h->stream;
+  const int64_t n = ep.num_tiles, G = h->sm_count;
+  if (n < 4 * G) return;
+  std::vector<int64_t> src, dst;
+  std::vector<int32_t> len;
+  int64_t f = 0, e = n, d = 0;
+  for (int64_t b = 0; f < e; ++b) {
+    const int64_t l = std::min<int64_t>(G, e - f);
+    if (b % 2 == 0) { src.push_back(f); f += l; }
+    else { e -= l; src.push_back(e); }
+    dst.push_back(d);
+    len.push_back(static_cast<int32_t>(l));
+    d += l;
+  }
+  const size_t nb = src.size();
+  dbuf<int64_t> d_src(nb, s), d_dst(nb, s);
+  dbuf<int32_t> d_len(nb, s);
+  CUDA_TRY(cudaMemcpyAsync(d_src.data(), src.data(), nb * 8, cudaMemcpyHostToDevice, s));
+  CUDA_TRY(cudaMemcpyAsync(d_dst.data(), dst.data(), nb * 8, cudaMemcpyHostToDevice, s));
+  CUDA_TRY(cudaMemcpyAsync(d_len.data(), len.data(), nb * 4, cudaMemcpyHostToDevice, s));
+  dbuf<tile_t> out(static_cast<size_t>(n), s);
+  permute_tile_blocks_kernel<<<static_cast<unsigned>(nb), 128, 0, s>>>(
+    ep.tiles.data(), out.data(), d_src.data(), d_dst.data(), d_len.data());
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaStreamSynchronize(s));
+  ep.tiles = std::move(out);
+}
+
 // generic variant for multi-GPU partitions, whose rows follow the GLOBAL degree order: a greedy
 // pass over the offsets on the host packs complete rows into tiles of <= T edges and <= rowcap
 // rows; any row with >= kLongRow edges is chunked, wherever it sits
@@ -92,6 +132,7 @@ static void build_schedule_generic(b200_handle* h, edge_partition& ep, int T, in
     CUDA_TRY(cudaMemcpyAsync(ep.long_row_ids.data(), long_ids.data(), long_ids.size() * 4,
                              cudaMemcpyHostToDevice, s));
   CUDA_TRY(cudaStreamSynchronize(s));
+  interleave_tiles(h, ep);
   ep.sched_tile_edges = T;
   ep.sched_row_cap    = rowcap;
 }
@@ -168,6 +209,7 @@ static void build_schedule_t(b200_handle* h, edge_partition& ep, int T, int rowc
     CUDA_TRY(cudaGetLastError());
   }
   CUDA_TRY(cudaStreamSynchronize(s));
+  interleave_tiles(h, ep);
   ep.sched_tile_edges = T;
   ep.sched_row_cap    = rowcap;
 }

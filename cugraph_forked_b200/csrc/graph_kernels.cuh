@@ -261,6 +261,14 @@ __global__ void row_tiles_kernel(const ET* offsets, int64_t row_lo, int64_t row_
 }
 
 // first row in [row_lo, row_hi) whose degree is < dthr (degrees are non-increasing there)
+// tiles_out[dst_first[b] + k] = tiles_in[src_first[b] + k] for k < len[b]
+__global__ void permute_tile_blocks_kernel(const tile_t* in, tile_t* out, const int64_t* src_first,
+                                           const int64_t* dst_first, const int32_t* len)
+{
+  const int b = blockIdx.x;
+  for (int k = threadIdx.x; k < len[b]; k += blockDim.x) out[dst_first[b] + k] = in[src_first[b] + k];
+}
+
 template <typename ET>
 __global__ void degree_split_kernel(const ET* offsets, int64_t row_lo, int64_t row_hi, int64_t dthr,
                                     int64_t* out)
