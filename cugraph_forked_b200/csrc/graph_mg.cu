@@ -319,11 +319,11 @@ static void create_mg_t(b200_handle* h, const VT* src, const VT* dst, const void
       if (wsize == 4) {
         dbuf<float> w = shuffle<float>(h, h->world, P, h->rank, static_cast<const float*>(weights),
                                        ne_in, plan, recv);
-        e_w.p = reinterpret_cast<char*>(w.p); e_w.n = w.n * 4; w.p = nullptr; w.n = 0;
+        e_w.p = reinterpret_cast<char*>(w.p); e_w.n = w.n * 4; e_w.st = s; w.p = nullptr; w.n = 0;
       } else {
         dbuf<double> w = shuffle<double>(h, h->world, P, h->rank,
                                          static_cast<const double*>(weights), ne_in, plan, recv);
-        e_w.p = reinterpret_cast<char*>(w.p); e_w.n = w.n * 8; w.p = nullptr; w.n = 0;
+        e_w.p = reinterpret_cast<char*>(w.p); e_w.n = w.n * 8; e_w.st = s; w.p = nullptr; w.n = 0;
       }
     }
   }
@@ -661,6 +661,33 @@ void graph_create_mg(b200_handle* h, const void* src, const void* dst, const voi
                      size_t n_local_vertices, bool store_transposed, b200_graph* g)
 {
   B200_EXPECTS(h->world != nullptr, kInvalidHandle, "multi-GPU graph needs an MG handle");
+  // Weighted or not is a property of the whole graph (the reference passes an optional vector,
+  // present on every rank even when empty, graph_functions.hpp:463-478).  A rank that
+  // contributes no edges may hold a null pointer, so the ranks agree first: every rank must make
+  // the same sequence of exchanges.
+  dbuf<char> no_weights;
+  {
+    int64_t mine = ne == 0 ? 0 : (weights ? 2 + weight_type : 1);
+    std::vector<int64_t> all = allgather_host(h, h->world, h->size, {mine});
+    int64_t agreed = 0;
+    bool mixed     = false;
+    for (int64_t v : all) {
+      if (v == 0) continue;
+      if (agreed == 0) agreed = v;
+      else if (agreed != v) mixed = true;
+    }
+    B200_EXPECTS(!mixed, kInvalidInput,
+                 "Invalid input argument: every rank must pass weights of one type, or none.");
+    if (agreed >= 2) {
+      weight_type = static_cast<int>(agreed - 2);
+      if (!weights) {
+        no_weights.alloc(8, h->stream);
+        weights = no_weights.data();
+      }
+    } else if (agreed == 1) {
+      weights = nullptr;
+    }
+  }
   g->vertex_type      = vertex_type;
   g->weight_type      = weights ? weight_type : B200_FLOAT32;
   g->weighted         = weights != nullptr;

@@ -158,6 +158,31 @@ def run(scale: int, edge_factor: int, dtype, weighted: bool, handle, rank, world
               f"katz_err={errk:.2e} eig_err={erre:.2e} ppr_err={errp:.2e}", flush=True)
 
 
+def run_tiny(handle, rank, world):
+    """The 6-vertex golden graph of c_api/mg_pagerank_test.c:213-247 on any number of ranks: most
+    ranks own one vertex or none and hold no edges at all (empty partitions, empty exchanges)."""
+    from cugraph_forked_b200 import engine
+    from oracle import graph_oracle as go
+    from tests import golden_vectors as gv
+    src, dst, wgt = gv.G6_SRC, gv.G6_DST, gv.G6_WGT
+    # every edge enters through rank 0; the other ranks contribute nothing
+    sel = slice(0, len(src)) if rank == 0 else slice(0, 0)
+    t = lambda a: torch.as_tensor(a[sel]).cuda()
+    g = engine.Graph(handle, t(src), t(dst), t(wgt), multi_gpu=True)
+    oracle = go.build_mg(src, dst, wgt, world)
+    check_graph(g, oracle, rank, True)
+    p = gv.G6_PAGERANK
+    pr, st = engine.pagerank(g, alpha=p["alpha"], epsilon=p["epsilon"],
+                             max_iterations=p["max_iterations"])
+    labels = oracle["labels"][rank]
+    assert gv.nearly_equal(pr.cpu().numpy(), p["result"][labels])
+    k = gv.G6_KATZ
+    kz, _ = engine.katz_centrality(g, alpha=k["alpha"], beta=k["beta"], epsilon=k["epsilon"],
+                                   max_iterations=k["max_iterations"], normalize=True)
+    assert gv.nearly_equal(kz.cpu().numpy(), k["result"][labels])
+    print(f"MG_WORKER_OK rank={rank}/{world} tiny graph: local vertices {len(labels)}", flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--scale", type=int, default=12)
@@ -172,6 +197,7 @@ def main():
         dist.barrier()
     for dtype, weighted in ((np.float32, False), (np.float64, True), (np.float32, True)):
         run(args.scale, args.edge_factor, dtype, weighted, handle, rank, world)
+    run_tiny(handle, rank, world)
     # a graph with long rows in every partition (hubs) and many empty rows
     run(args.scale + 2, 8, np.float32, False, handle, rank, world)
 

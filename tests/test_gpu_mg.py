@@ -32,6 +32,11 @@ def test_mg_world_size_1(mg1, dtype, weighted):
     mg_worker.run(11, 16, dtype, weighted, mg1, 0, 1, verbose=False)
 
 
+def test_mg_tiny_graph_world_size_1(mg1):
+    from tests import mg_worker
+    mg_worker.run_tiny(mg1, 0, 1)
+
+
 def test_mg_c_api_world_size_1(mg1):
     """cugraph_mg_graph_create + cugraph_pagerank through the pylibcugraph mirror on an MG
     handle (c_api/mg_pagerank_test.c:213-247 golden vector)."""
@@ -63,4 +68,4 @@ def test_mg_torchrun(world, oracle_built):
            str(29500 + world), os.path.join(ROOT, "tests", "mg_worker.py"), "--scale", "12"]
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=900)
     ok = r.stdout.count("MG_WORKER_OK")
-    assert r.returncode == 0 and ok == 4 * world, (r.stdout[-3000:], r.stderr[-3000:])
+    assert r.returncode == 0 and ok == 5 * world, (r.stdout[-3000:], r.stderr[-3000:])
