@@ -8,6 +8,9 @@
 #include <cmath>
 #include <cstdlib>
 
+#include <climits>
+
+#include "banded.cuh"
 #include "centrality.cuh"
 #include "spmv.cuh"
 
@@ -61,6 +64,9 @@ template <> struct alt_cfg<3> { using type = pull_cfg<4096, 3, 512>; };
 template <> struct alt_cfg<4> { using type = pull_cfg<4096, 5, 512>; };
 template <> struct alt_cfg<5> { using type = pull_cfg<8192, 2, 1024>; };
 constexpr int kNumAltCfg = 6;
+
+// the two-phase banded path (banded.cuh) is opt-in until measured: B200_BANDED=1
+constexpr int kBandedDefault = 0;
 
 int env_int(const char* name, int dflt)
 {
@@ -129,6 +135,12 @@ struct pull_launcher {
   int cfg_id{0};
   bool tiled{false};
   int64_t launches{0};
+  // two-phase path (banded.cuh): phase 1 pre-reduces the cells of the hot bands from shared
+  // memory into `pval`, phase 2 runs the tiled kernel over the reduced partition `kp`
+  banded_layout* banded{nullptr};
+  edge_partition* kp{nullptr};   // the partition the tiled kernel walks (ep or the reduced one)
+  dbuf<RT> pval;
+  const RT* kweights{nullptr};   // weights of kp
 
   void init(b200_handle* h_, b200_graph* g, edge_partition* ep_);
 
@@ -197,8 +209,31 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
     T      = ts[cfg_id];
     rowcap = rs[cfg_id];
   }
+  kp       = ep;
+  kweights = weights;
+  banded   = nullptr;
+  if (tiled && !g->multi_gpu && !ep->generic_schedule && !ep->offsets64 &&
+      env_int("B200_BANDED", kBandedDefault) != 0) {
+    banded_layout* bl = banded_get<RT>(h, *ep, weights, T, rowcap);
+    if (bl && bl->enabled) {
+      banded   = bl;
+      kp       = bl->reduced.get();
+      kweights = weighted ? reinterpret_cast<const RT*>(kp->weights.data()) : nullptr;
+      pval.alloc(static_cast<size_t>(bl->num_partials), s, 8);
+      static bool configured = false;
+      if (!configured) {
+        CUDA_TRY(cudaFuncSetAttribute(band_reduce_kernel<RT, true>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      band_geom<RT>::entries * static_cast<int>(sizeof(RT))));
+        CUDA_TRY(cudaFuncSetAttribute(band_reduce_kernel<RT, false>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      band_geom<RT>::entries * static_cast<int>(sizeof(RT))));
+        configured = true;
+      }
+    }
+  }
   if (tiled) {
-    build_schedule(h, *ep, T, rowcap);
+    if (!banded) build_schedule(h, *ep, T, rowcap);
     main_ctas = h->sm_count;  // one persistent warp-specialised CTA per SM
     // A CTA of this kernel takes the whole register file of its SM, so NCCL's kernels cannot
     // share an SM with it.  On a multi-GPU grid the per-partition reductions run on a second
@@ -208,16 +243,16 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
       const bool fused = !g->fused.empty() && ep == &g->fused[0];
       main_ctas = std::max(1, main_ctas - std::max(0, env_int("B200_MG_RESERVED_SMS", fused ? 4 : 16)));
     }
-    if (ep->num_tiles < main_ctas) main_ctas = static_cast<int>(std::max<int64_t>(ep->num_tiles, 1));
+    if (kp->num_tiles < main_ctas) main_ctas = static_cast<int>(std::max<int64_t>(kp->num_tiles, 1));
     // tail kernel: 8 lanes per long row, 32 rows per 256-thread block
-    int64_t want_tail = div_up(std::max<int64_t>(ep->num_long_rows, 1), 32);
+    int64_t want_tail = div_up(std::max<int64_t>(kp->num_long_rows, 1), 32);
     tail_ctas         = static_cast<int>(std::min<int64_t>(want_tail, 8 * h->sm_count));
   } else {
     main_ctas = h->sm_count * 8;
     tail_ctas = 1;
   }
   slots = main_ctas + tail_ctas;
-  chunk_partials.alloc(static_cast<size_t>(std::max<int64_t>(ep->num_chunks, 1)), s);
+  chunk_partials.alloc(static_cast<size_t>(std::max<int64_t>(kp->num_chunks, 1)), s);
   cta_partials.alloc(static_cast<size_t>(2 * slots), s);
   CUDA_TRY(cudaMemsetAsync(cta_partials.data(), 0, sizeof(double) * 2 * slots, s));
 }
@@ -246,19 +281,46 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
     ++launches;
     return;
   }
+  if (banded) {
+    // phase 1: pre-reduce the cells of the hot bands from shared memory
+    band_params B{};
+    B.x               = x;
+    B.pval            = pval.data();
+    B.bidx            = banded->bidx.data();
+    B.bw              = weighted ? banded->bw.data() : nullptr;
+    B.ppos            = banded->ppos.data();
+    B.tasks           = banded->tasks.data();
+    B.groups          = banded->groups.data();
+    B.cta_group_first = banded->cta_group_first.data();
+    B.num_minors      = ep->num_minors;
+    B.state           = state;
+    const size_t smem = static_cast<size_t>(band_geom<RT>::entries) * sizeof(RT);
+    if (weighted)
+      band_reduce_kernel<RT, true><<<banded->num_ctas, kBandThreads, smem, s>>>(B);
+    else
+      band_reduce_kernel<RT, false><<<banded->num_ctas, kBandThreads, smem, s>>>(B);
+    CUDA_TRY(cudaGetLastError());
+    ++launches;
+  }
   pull_params P{};
-  P.tiles          = ep->tiles.data();
-  P.num_tiles      = ep->num_tiles;
-  P.offsets        = ep->offsets.data();
-  P.indices        = ep->indices.data();
-  P.weights        = weights;
+  P.tiles          = kp->tiles.data();
+  P.num_tiles      = kp->num_tiles;
+  P.offsets        = kp->offsets.data();
+  P.indices        = kp->indices.data();
+  P.weights        = kweights;
   P.x              = x;
-  P.zero_first     = ep->zero_first;
-  P.num_rows       = ep->num_rows;
+  P.x_hi           = nullptr;
+  P.x_split        = INT_MAX;
+  P.zero_first     = kp->zero_first;
+  P.num_rows       = kp->num_rows;
   P.chunk_partials = chunk_partials.data();
   P.cta_partials   = parts;
   P.slots          = slots;
   P.state          = state;
+  if (banded) {
+    P.x_hi    = pval.data();
+    P.x_split = banded->x_split;
+  }
   const int hub_cap = env_int("B200_HUB_ENTRIES", 1 << 30);
   auto launch = [&](auto et, auto wtag, auto cfgtag) {
     using ET         = decltype(et);
@@ -270,7 +332,7 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
     // lines to track the outstanding gathers (profiles/microbench_gather.md)
     const int64_t budget = static_cast<int64_t>(env_int("B200_SMEM_BUDGET_KB", 160)) * 1024;
     int64_t room = std::max<int64_t>(0, budget - static_cast<int64_t>(SM::ring)) / sizeof(RT);
-    int hub = static_cast<int>(std::min<int64_t>({ep->num_minors, SM::max_hub, room})) & ~31;
+    int hub = static_cast<int>(std::min<int64_t>({kp->num_minors, SM::max_hub, room})) & ~31;
     hub     = std::max(0, std::min(hub, hub_cap));
     static bool configured = false;
     if (!configured) {
@@ -279,8 +341,8 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
       configured = true;
     }
     // split the cache between the pieces of the minor range (one piece on a single GPU)
-    std::vector<int64_t> pieces = ep->minor_piece_offsets;
-    if (pieces.size() < 2 || pieces.size() - 1 > kMaxHubPieces) pieces = {0, ep->num_minors};
+    std::vector<int64_t> pieces = kp->minor_piece_offsets;
+    if (pieces.size() < 2 || pieces.size() - 1 > kMaxHubPieces) pieces = {0, kp->num_minors};
     const int np  = static_cast<int>(pieces.size()) - 1;
     int total     = 0;
     P.hub_pieces  = np;
@@ -309,7 +371,7 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
     }
     launch(et, wtag, default_cfg<RT, W>{});
   };
-  if (ep->offsets64) {
+  if (kp->offsets64) {
     if (weighted) go(int64_t{}, std::true_type{}); else go(int64_t{}, std::false_type{});
   } else {
     if (weighted) go(int32_t{}, std::true_type{}); else go(int32_t{}, std::false_type{});
@@ -324,10 +386,10 @@ void pull_launcher<RT>::tail(EPI const& epi, iter_state* state, double epsilon, 
                              bool check, bool finalize)
 {
   tail_params P{};
-  P.long_row_ids         = (tiled && ep->generic_schedule) ? ep->long_row_ids.data() : nullptr;
-  P.long_row_chunk_first = tiled ? ep->long_row_chunk_first.data() : nullptr;
+  P.long_row_ids         = (tiled && kp->generic_schedule) ? kp->long_row_ids.data() : nullptr;
+  P.long_row_chunk_first = tiled ? kp->long_row_chunk_first.data() : nullptr;
   P.chunk_partials       = chunk_partials.data();
-  P.num_long_rows        = tiled ? ep->num_long_rows : 0;
+  P.num_long_rows        = tiled ? kp->num_long_rows : 0;
   P.cta_partials         = finalize ? cta_partials.data() : nullptr;
   P.slots                = slots;
   P.main_ctas            = main_ctas;

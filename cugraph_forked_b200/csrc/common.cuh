@@ -9,6 +9,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <memory>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -166,6 +167,8 @@ struct b200_handle {
 
 namespace b200 {
 
+struct banded_layout;  // banded.cuh: the pre-reduction layout derived from a CSC rectangle
+
 // One CSC (or CSR) rectangle + its kernel schedule.
 struct edge_partition {
   int64_t num_rows{0};          // majors in this partition
@@ -196,6 +199,9 @@ struct edge_partition {
   // order: offsets of those pieces inside the range ({0, num_minors} on a single GPU).  The
   // kernel's shared-memory hub cache takes the head of every piece.
   std::vector<int64_t> minor_piece_offsets;
+  // banded pre-reduction layouts derived from this rectangle, one per result width
+  // ([0] 4-byte, [1] 8-byte values), built on first use by the pull launcher (banded.cu)
+  std::shared_ptr<banded_layout> banded[2];
 };
 
 }  // namespace b200

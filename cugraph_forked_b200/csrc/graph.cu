@@ -12,6 +12,7 @@
 // order at once.
 #include <cstdlib>
 
+#include "banded.cuh"
 #include "graph.cuh"
 #include "graph_kernels.cuh"
 
@@ -219,6 +220,160 @@ void build_schedule(b200_handle* h, edge_partition& ep, int T, int rowcap)
   if (ep.sched_tile_edges == T && ep.sched_row_cap == rowcap) return;
   if (ep.offsets64) build_schedule_t<int64_t>(h, ep, T, rowcap);
   else build_schedule_t<int32_t>(h, ep, T, rowcap);
+}
+
+// ------------------------------------------------------------------------------------------
+// schedule of a REDUCED partition (banded.cuh): rows keep their ids but their entry counts are
+// no longer monotone.  Rows [0, n_long) (the original high-degree segment, a few ten thousand
+// rows) are packed on the host exactly like the generic schedule; rows [n_long, n_nz) all have
+// fewer than kLongRow entries and are packed on the device: window k of T entries owns the
+// rows whose first entry lies in it, cut into tiles of <= rowcap rows.
+// ------------------------------------------------------------------------------------------
+namespace {
+
+__global__ void window_first_rows_kernel(const int32_t* off, int64_t row_lo, int64_t row_hi,
+                                         int64_t edge_lo, int T, int64_t nwin, int64_t* first_row)
+{
+  int64_t k = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  if (k > nwin) return;
+  if (k == nwin) { first_row[k] = row_hi; return; }
+  const int64_t target = edge_lo + k * T;
+  int64_t lo = row_lo, hi = row_hi;
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if (static_cast<int64_t>(off[mid]) < target) lo = mid + 1;
+    else hi = mid;
+  }
+  first_row[k] = lo;
+}
+
+__global__ void window_tile_counts_kernel(const int64_t* first_row, int64_t nwin, int rowcap,
+                                          uint32_t* counts)
+{
+  int64_t k = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  if (k >= nwin) return;
+  const int64_t rows = first_row[k + 1] - first_row[k];
+  counts[k] = static_cast<uint32_t>((rows + rowcap - 1) / rowcap);
+}
+
+__global__ void window_tiles_kernel(const int32_t* off, const int64_t* first_row,
+                                    const uint32_t* tile_base, int64_t nwin, int rowcap,
+                                    tile_t* tiles)
+{
+  int64_t k = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  if (k >= nwin) return;
+  const int64_t r_end = first_row[k + 1];
+  uint32_t j          = tile_base[k];
+  for (int64_t r0 = first_row[k]; r0 < r_end; r0 += rowcap, ++j) {
+    const int64_t r1 = min(r_end, r0 + rowcap);
+    tile_t t;
+    t.edge_first = static_cast<int64_t>(off[r0]);
+    t.num_edges  = static_cast<int32_t>(static_cast<int64_t>(off[r1]) - t.edge_first);
+    t.row_first  = static_cast<int32_t>(r0);
+    t.num_rows   = static_cast<int32_t>(r1 - r0);
+    t.aux        = 0;
+    t.kind       = 0;
+    t.pad        = 0;
+    tiles[j]     = t;
+  }
+}
+
+}  // namespace
+
+void build_schedule_reduced(b200_handle* h, edge_partition& rp, int64_t n_long, int64_t n_nz, int T,
+                            int rowcap)
+{
+  cudaStream_t s = h->stream;
+  B200_EXPECTS(!rp.offsets64, kInvalidInput, "reduced partitions use 32-bit offsets");
+  const int32_t* off = reinterpret_cast<const int32_t*>(rp.offsets.data());
+  n_long = std::min(n_long, n_nz);
+  // ---- host: rows [0, n_long) ----
+  std::vector<int32_t> h_off(static_cast<size_t>(n_long) + 1, 0);
+  int32_t h_end = 0;
+  CUDA_TRY(cudaMemcpyAsync(h_off.data(), off, h_off.size() * 4, cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaMemcpyAsync(&h_end, off + n_nz, 4, cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(cudaStreamSynchronize(s));
+  std::vector<tile_t> chunk_tiles, row_tiles;
+  std::vector<int64_t> chunk_first;
+  std::vector<int32_t> long_ids;
+  tile_t cur{};
+  auto flush = [&] {
+    if (cur.num_rows > 0) row_tiles.push_back(cur);
+    cur = tile_t{};
+  };
+  for (int64_t r = 0; r < n_long; ++r) {
+    const int64_t b = h_off[r], e = h_off[r + 1], d = e - b;
+    if (d >= kLongRow) {
+      flush();
+      long_ids.push_back(static_cast<int32_t>(r));
+      chunk_first.push_back(static_cast<int64_t>(chunk_tiles.size()));
+      for (int64_t c = b; c < e; c += T) {
+        tile_t t{};
+        t.edge_first = c;
+        t.num_edges  = static_cast<int32_t>(std::min<int64_t>(T, e - c));
+        t.row_first  = static_cast<int32_t>(r);
+        t.num_rows   = 1;
+        t.aux        = static_cast<int32_t>(chunk_tiles.size());
+        t.kind       = 1;
+        chunk_tiles.push_back(t);
+      }
+      continue;
+    }
+    if (cur.num_rows == rowcap || cur.num_edges + d > T) flush();
+    if (cur.num_rows == 0) {
+      cur.edge_first = b;
+      cur.row_first  = static_cast<int32_t>(r);
+    }
+    cur.num_rows += 1;
+    cur.num_edges += static_cast<int32_t>(d);
+  }
+  flush();
+  chunk_first.push_back(static_cast<int64_t>(chunk_tiles.size()));
+  // ---- device: rows [n_long, n_nz) ----
+  const int64_t edge_lo = h_off[n_long], edge_hi = h_end;
+  const int64_t nwin    = (n_nz > n_long) ? std::max<int64_t>(div_up(edge_hi - edge_lo, T), 1) : 0;
+  dbuf<int64_t> first_row(static_cast<size_t>(nwin) + 1, s);
+  dbuf<uint32_t> counts(static_cast<size_t>(nwin) + 1, s);
+  uint32_t n_win_tiles = 0;
+  if (nwin > 0) {
+    window_first_rows_kernel<<<grid_for(nwin + 1), kThreads, 0, s>>>(off, n_long, n_nz, edge_lo, T,
+                                                                     nwin, first_row.data());
+    window_tile_counts_kernel<<<grid_for(nwin), kThreads, 0, s>>>(first_row.data(), nwin, rowcap,
+                                                                  counts.data());
+    CUDA_TRY(cudaGetLastError());
+    exclusive_scan<uint32_t, uint32_t>(counts.data(), counts.data(), static_cast<size_t>(nwin), s,
+                                       true);
+    CUDA_TRY(cudaMemcpyAsync(&n_win_tiles, counts.data() + nwin, 4, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+  }
+  rp.num_chunks    = static_cast<int64_t>(chunk_tiles.size());
+  rp.num_long_rows = static_cast<int64_t>(long_ids.size());
+  rp.zero_first    = n_nz;
+  rp.num_tiles     = rp.num_chunks + static_cast<int64_t>(row_tiles.size()) + n_win_tiles;
+  rp.tiles.alloc(static_cast<size_t>(std::max<int64_t>(rp.num_tiles, 1)), s);
+  if (!chunk_tiles.empty())
+    CUDA_TRY(cudaMemcpyAsync(rp.tiles.data(), chunk_tiles.data(), chunk_tiles.size() * sizeof(tile_t),
+                             cudaMemcpyHostToDevice, s));
+  if (!row_tiles.empty())
+    CUDA_TRY(cudaMemcpyAsync(rp.tiles.data() + chunk_tiles.size(), row_tiles.data(),
+                             row_tiles.size() * sizeof(tile_t), cudaMemcpyHostToDevice, s));
+  if (n_win_tiles > 0) {
+    window_tiles_kernel<<<grid_for(nwin), kThreads, 0, s>>>(
+      off, first_row.data(), counts.data(), nwin, rowcap,
+      rp.tiles.data() + chunk_tiles.size() + row_tiles.size());
+    CUDA_TRY(cudaGetLastError());
+  }
+  rp.long_row_chunk_first.alloc(chunk_first.size(), s);
+  CUDA_TRY(cudaMemcpyAsync(rp.long_row_chunk_first.data(), chunk_first.data(),
+                           chunk_first.size() * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+  rp.long_row_ids.alloc(std::max<size_t>(long_ids.size(), 1), s);
+  if (!long_ids.empty())
+    CUDA_TRY(cudaMemcpyAsync(rp.long_row_ids.data(), long_ids.data(), long_ids.size() * 4,
+                             cudaMemcpyHostToDevice, s));
+  CUDA_TRY(cudaStreamSynchronize(s));
+  interleave_tiles(h, rp);
+  rp.sched_tile_edges = T;
+  rp.sched_row_cap    = rowcap;
 }
 
 // ------------------------------------------------------------------------------------------

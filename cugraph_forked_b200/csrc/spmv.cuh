@@ -45,6 +45,10 @@ struct pull_params {
   const int32_t* indices;  // padded by >= 16 bytes
   const void* weights;     // RT or nullptr
   const void* x;           // gathered vector, RT
+  // second piece of the gathered vector (banded.cuh): an index >= x_split reads
+  // x_hi[index - x_split] (the partial sums of the pre-reduced cells); INT32_MAX = none
+  const void* x_hi;
+  int32_t x_split;
   int64_t zero_first;      // rows [zero_first, num_rows) have no edges (epilogue only)
   int64_t num_rows;
   double* chunk_partials;  // [num_chunks]
@@ -153,6 +157,9 @@ __global__ void __launch_bounds__(kPullThreads, 1)
   const ET* offsets    = static_cast<const ET*>(P.offsets);
   const RT* weights    = static_cast<const RT*>(P.weights);
   const RT* x          = static_cast<const RT*>(P.x);
+  const int x_split    = P.x_split;
+  // pre-offset so that both pieces are addressed with the index itself
+  const RT* x_hi       = static_cast<const RT*>(P.x_hi) - (P.x_hi ? x_split : 0);
   const int64_t stride = gridDim.x;
   const int64_t my_n =
     (P.num_tiles > blockIdx.x) ? (P.num_tiles - blockIdx.x + stride - 1) / stride : 0;
@@ -282,7 +289,7 @@ __global__ void __launch_bounds__(kPullThreads, 1)
     // critical path, the gather warps' tail is not).
     auto gather1 = [&](int id) -> RT {
       const int sl = hub_slot(id);
-      return sl >= 0 ? hub[sl] : ld_gather(x + id);
+      return sl >= 0 ? hub[sl] : ld_gather((id >= x_split ? x_hi : x) + id);
     };
 #endif
     // Rolling software pipeline: a lane issues the four gathers of its next quad (possibly of
