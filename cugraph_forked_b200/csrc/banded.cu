@@ -16,7 +16,7 @@
 //   5. band-major arrays: 16-bit band-local index | cell-start flag, weights, and for every
 //      cell (in band-major order) the slot of its partial;
 //   6. tasks = the cells that start inside one window of kTaskWindow edges of a band; the host
-//      splits the task list into contiguous, cost-balanced ranges, one per SM.
+//      cuts the task list into the units of the kernel's work queue.
 #include <chrono>
 #include <cstdlib>
 
@@ -379,55 +379,29 @@ static void build_banded(b200_handle* h, edge_partition& ep, const RT* w, banded
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaStreamSynchronize(s));
   }
-  // contiguous cost-balanced ranges: cost = edges of the window + a band load whenever the CTA
-  // has to switch bands
+  // the work queue: units of consecutive tasks of one band in band order (a CTA that claims
+  // consecutive units keeps its band in shared memory); unit sizes follow guided
+  // self-scheduling, remaining / (2 * CTAs) clamped to [kUnitMin, kUnitMax] tasks, so that the
+  // last units are small and the CTAs finish together
   const int nctas = h->sm_count;
-  int64_t total_cost = 0;
-  {
-    int32_t last = -1;
-    for (int64_t k = 0; k < ntasks; ++k) {
-      total_cost += win_hi[k] - win_lo[k];
-      if (win_band[k] != last) { total_cost += kBandLoadCost; last = win_band[k]; }
-    }
-  }
-  const int64_t target = (total_cost + int64_t(nctas) * kBandLoadCost) / nctas + 1;
+  constexpr int64_t kUnitMin = 32, kUnitMax = 512;
   std::vector<band_group> groups;
-  std::vector<int32_t> cta_first(static_cast<size_t>(nctas) + 1, 0);
-  {
-    int c = 0;
-    int64_t acc = 0;
-    cta_first[0] = 0;
-    for (int64_t k = 0; k < ntasks; ++k) {
-      const int64_t edges = win_hi[k] - win_lo[k];
-      const bool cta_empty = static_cast<int32_t>(groups.size()) == cta_first[c];
-      bool new_group = cta_empty || groups.back().band != win_band[k];
-      int64_t cost   = edges + (new_group ? kBandLoadCost : 0);
-      if (!cta_empty && acc + cost > target && c < nctas - 1) {
-        ++c;
-        cta_first[c] = static_cast<int32_t>(groups.size());
-        acc          = 0;
-        new_group    = true;
-        cost         = edges + kBandLoadCost;
-      }
-      if (new_group) {
-        band_group gpp{};
-        gpp.task_first = static_cast<int32_t>(k);
-        gpp.task_end   = static_cast<int32_t>(k);
-        gpp.band       = win_band[k];
-        groups.push_back(gpp);
-      }
-      groups.back().task_end = static_cast<int32_t>(k + 1);
-      acc += cost;
-    }
-    for (int i = c + 1; i <= nctas; ++i) cta_first[i] = static_cast<int32_t>(groups.size());
+  for (int64_t k = 0; k < ntasks;) {
+    int64_t size = std::max<int64_t>(kUnitMin, std::min<int64_t>(kUnitMax, (ntasks - k) / (2 * nctas)));
+    int64_t e    = std::min<int64_t>(ntasks, k + size);
+    for (int64_t j = k + 1; j < e; ++j)
+      if (win_band[j] != win_band[k]) { e = j; break; }
+    band_group gpp{};
+    gpp.task_first = static_cast<int32_t>(k);
+    gpp.task_end   = static_cast<int32_t>(e);
+    gpp.band       = win_band[k];
+    groups.push_back(gpp);
+    k = e;
   }
   L.num_groups = static_cast<int64_t>(groups.size());
   L.num_ctas   = nctas;
   L.groups.alloc(groups.size(), s);
-  L.cta_group_first.alloc(cta_first.size(), s);
   CUDA_TRY(cudaMemcpyAsync(L.groups.data(), groups.data(), groups.size() * sizeof(band_group),
-                           cudaMemcpyHostToDevice, s));
-  CUDA_TRY(cudaMemcpyAsync(L.cta_group_first.data(), cta_first.data(), cta_first.size() * 4,
                            cudaMemcpyHostToDevice, s));
   CUDA_TRY(cudaStreamSynchronize(s));
 

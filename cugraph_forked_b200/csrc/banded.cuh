@@ -53,7 +53,9 @@ struct alignas(8) band_task {
 };
 static_assert(sizeof(band_task) == 24, "band_task layout");
 
-// tasks [task_first, task_end) of one band, run by one CTA with the band in shared memory
+// one unit of the work queue: tasks [task_first, task_end) of one band, run by one CTA with the
+// band in shared memory.  CTAs claim units in order with a global counter; unit sizes shrink
+// towards the end of the queue (guided self-scheduling).
 struct band_group {
   int32_t task_first;
   int32_t task_end;
@@ -75,8 +77,7 @@ struct banded_layout {
   dbuf<char> bw;                // RT [num_banded_edges + pad], weighted graphs only
   dbuf<int32_t> ppos;           // [num_partials] band-major cell rank -> partial slot (row-major)
   dbuf<band_task> tasks;
-  dbuf<band_group> groups;
-  dbuf<int32_t> cta_group_first;  // [num_ctas + 1]
+  dbuf<band_group> groups;        // the work queue: units of consecutive tasks of one band
   std::unique_ptr<edge_partition> reduced;  // phase-2 CSC + its tile schedule
   double build_ms{0.0};
 };
@@ -89,39 +90,63 @@ struct band_params {
   const int32_t* ppos;
   const band_task* tasks;
   const band_group* groups;
-  const int32_t* cta_group_first;
+  int32_t num_groups;
+  int32_t* queue;                 // this launch's unit counter (0 at launch)
+  int32_t* queue_next;            // the next launch's counter, reset by this launch
   int64_t num_minors;
   const iter_state* state;        // may be nullptr
 };
 
 // ------------------------------------------------------------------------------------------
-// phase-1 kernel: one persistent CTA per SM.  For each of its groups the CTA loads the band of
-// x into shared memory; its 32 warps then claim the group's tasks.  A warp walks a task in
+// phase-1 kernel: one persistent CTA per SM.  A CTA claims the next unit of the work queue,
+// loads the unit's band of x into shared memory unless it already holds it (units are queued
+// in band order), and its 32 warps then claim the unit's tasks.  A warp walks a task in
 // steps of 256 edges (lane l owns edges [8l, 8l + 8) of the step): one 128-bit load of eight
 // 16-bit indices (prefetched a step ahead), eight shared-memory gathers, a sequential
 // segmented sum inside the lane, a segmented warp scan of the lanes' open tails, and one store
 // per cell that ends in the lane.  The sum that is still open at the end of a step is carried
 // in a register to the next step.
 // ------------------------------------------------------------------------------------------
+// flag bits (bit 15 of every 16-bit index) of the eight indices of a 128-bit load -> bits 0..7
+__device__ __forceinline__ uint32_t band_flag_bits(uint4 const& c)
+{
+  // bytes 1 and 3 of every word carry the flags in their top bit
+  const uint32_t lo = __byte_perm(c.x, c.y, 0x7531);  // [x.b1, x.b3, y.b1, y.b3]
+  const uint32_t hi = __byte_perm(c.z, c.w, 0x7531);
+  const uint32_t a  = ((lo >> 7) & 0x01010101u) * 0x01020408u;  // bits 24..27 = the four flags
+  const uint32_t b  = ((hi >> 7) & 0x01010101u) * 0x01020408u;
+  return (a >> 24) | ((b >> 24) << 4);
+}
+
 template <typename RT, bool WEIGHTED>
 __global__ void __launch_bounds__(kBandThreads, 1) band_reduce_kernel(const __grid_constant__ band_params P)
 {
   using G = band_geom<RT>;
+  static_assert(kMinCell >= 3, "a lane of 8 consecutive edges must hold at most 3 cell starts");
   extern __shared__ __align__(16) unsigned char band_smem[];
   RT* band = reinterpret_cast<RT*>(band_smem);
   __shared__ int s_next;
+  __shared__ int s_unit;
 
-  if (P.state && P.state->done) return;
   const int tid = threadIdx.x, lane = tid & 31;
+  // the other queue counter is the next launch's: reset it (stream order makes this safe)
+  if (blockIdx.x == 0 && tid == 0) *P.queue_next = 0;
+  if (P.state && P.state->done) return;
+  const uint32_t lanes_lt = (1u << lane) - 1u;
   const RT* x   = static_cast<const RT*>(P.x);
   RT* pval      = static_cast<RT*>(P.pval);
   const RT* bw  = static_cast<const RT*>(P.bw);
 
-  const int g0 = P.cta_group_first[blockIdx.x], g1 = P.cta_group_first[blockIdx.x + 1];
-  for (int g = g0; g < g1; ++g) {
-    const band_group grp = P.groups[g];
-    __syncthreads();  // every warp is done with the previous band
-    {
+  int cur_band = -1;
+  for (;;) {
+    __syncthreads();  // every warp is done with the previous unit
+    if (tid == 0) s_unit = atomicAdd(P.queue, 1);
+    __syncthreads();
+    const int u = s_unit;
+    if (u >= P.num_groups) break;
+    const band_group grp = P.groups[u];
+    if (grp.band != cur_band) {
+      cur_band            = grp.band;
       const int64_t first = static_cast<int64_t>(grp.band) << G::bits;
       const int64_t left  = P.num_minors - first;
       const int n         = static_cast<int>(left < G::entries ? left : G::entries);
@@ -136,8 +161,8 @@ __global__ void __launch_bounds__(kBandThreads, 1) band_reduce_kernel(const __gr
       } else {
         for (int i = tid; i < n; i += kBandThreads) band[i] = src[i];
       }
-      if (tid == 0) s_next = grp.task_first;
     }
+    if (tid == 0) s_next = grp.task_first;
     __syncthreads();
     for (;;) {
       int ti = 0;
@@ -150,110 +175,116 @@ __global__ void __launch_bounds__(kBandThreads, 1) band_reduce_kernel(const __gr
       const int total    = lead + t.count;
       const int steps    = (total + kStepEdges - 1) / kStepEdges;
       const uint16_t* ip = P.bidx + a0 + lane * 8;
-      int64_t rank       = t.rank_first;   // rank of the next cell start this warp will meet
+      const int32_t* pp  = P.ppos + t.rank_first;   // slots of this task's cells
+      int rank           = 0;              // cell starts met so far (relative to rank_first)
       RT carry           = RT(0);          // sum of the cell that is open at the step boundary
       uint4 cur          = __ldcs(reinterpret_cast<const uint4*>(ip));
       for (int st = 0; st < steps; ++st) {
         uint4 nxt = make_uint4(0, 0, 0, 0);
         if (st + 1 < steps) nxt = __ldcs(reinterpret_cast<const uint4*>(ip + (st + 1) * kStepEdges));
         const int base = st * kStepEdges + lane * 8;   // position of the lane's first edge
-        uint32_t h[8];
-        h[0] = cur.x & 0xffffu; h[1] = cur.x >> 16; h[2] = cur.y & 0xffffu; h[3] = cur.y >> 16;
-        h[4] = cur.z & 0xffffu; h[5] = cur.z >> 16; h[6] = cur.w & 0xffffu; h[7] = cur.w >> 16;
-        uint32_t fmask = 0, vmask = 0;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const bool valid = (base + i >= lead) && (base + i < total);
-          vmask |= (valid ? 1u : 0u) << i;
-          fmask |= ((valid && (h[i] & 0x8000u)) ? 1u : 0u) << i;
-        }
-        // ranks of the lane's cell starts
-        const int cnt = __popc(fmask);
-        int incl      = cnt;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const int u = __shfl_up_sync(0xffffffffu, incl, o);
-          if (lane >= o) incl += u;
-        }
-        const int excl       = incl - cnt;
-        const int step_flags = __shfl_sync(0xffffffffu, incl, 31);
-        // slot of the cell that ENDS at each of the lane's cell starts (= the previous cell);
-        // loaded now, used after the gathers
-        int slot[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          slot[i] = -1;
-          if (fmask & (1u << i)) {
-            const int64_t r = rank + excl + __popc(fmask & ((1u << i) - 1u)) - 1;
-            if (r >= t.rank_first) slot[i] = __ldg(P.ppos + r);
-          }
-        }
-        // gathers from the band
+        // gathers from the band (every index is a valid band offset, also outside the task)
         RT v[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) v[i] = (vmask & (1u << i)) ? band[h[i] & G::mask] : RT(0);
+        v[0] = band[cur.x & G::mask]; v[1] = band[(cur.x >> 16) & G::mask];
+        v[2] = band[cur.y & G::mask]; v[3] = band[(cur.y >> 16) & G::mask];
+        v[4] = band[cur.z & G::mask]; v[5] = band[(cur.z >> 16) & G::mask];
+        v[6] = band[cur.w & G::mask]; v[7] = band[(cur.w >> 16) & G::mask];
+        uint32_t fmask = band_flag_bits(cur);
         if (WEIGHTED) {
-          if (vmask) {
-            const RT* wp = bw + a0 + base;
-            if constexpr (sizeof(RT) == 4) {
-              const float4 w0 = __ldcs(reinterpret_cast<const float4*>(wp));
-              const float4 w1 = __ldcs(reinterpret_cast<const float4*>(wp) + 1);
-              v[0] *= w0.x; v[1] *= w0.y; v[2] *= w0.z; v[3] *= w0.w;
-              v[4] *= w1.x; v[5] *= w1.y; v[6] *= w1.z; v[7] *= w1.w;
-            } else {
+          // the weight arrays are padded, so this never reads out of bounds
+          const RT* wp = bw + a0 + base;
+          if constexpr (sizeof(RT) == 4) {
+            const float4 w0 = __ldcs(reinterpret_cast<const float4*>(wp));
+            const float4 w1 = __ldcs(reinterpret_cast<const float4*>(wp) + 1);
+            v[0] *= w0.x; v[1] *= w0.y; v[2] *= w0.z; v[3] *= w0.w;
+            v[4] *= w1.x; v[5] *= w1.y; v[6] *= w1.z; v[7] *= w1.w;
+          } else {
 #pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const double2 w = __ldcs(reinterpret_cast<const double2*>(wp) + i);
-                v[2 * i] *= w.x; v[2 * i + 1] *= w.y;
-              }
+            for (int i = 0; i < 4; ++i) {
+              const double2 w = __ldcs(reinterpret_cast<const double2*>(wp) + i);
+              v[2 * i] *= w.x; v[2 * i + 1] *= w.y;
             }
           }
         }
-        // sequential segmented sum inside the lane: closev[i] = sum of the lane's edges since
-        // its previous cell start (or since the lane's first edge), taken at cell start i
-        RT closev[8];
+        if (base < lead || base + 8 > total) {
+          // first / last lanes of a task: mask what lies outside
+          uint32_t vmask = 0;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) vmask |= ((base + i >= lead && base + i < total) ? 1u : 0u) << i;
+          fmask &= vmask;
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            if (!(vmask & (1u << i))) v[i] = RT(0);
+        }
+        // ranks of the lane's cell starts: cells have >= kMinCell = 3 edges, so a lane holds at
+        // most 3 of them and two ballots give the exclusive prefix of the counts
+        const int cnt        = __popc(fmask);
+        const uint32_t b0    = __ballot_sync(0xffffffffu, cnt & 1);
+        const uint32_t b1    = __ballot_sync(0xffffffffu, cnt & 2);
+        const int excl       = __popc(b0 & lanes_lt) + 2 * __popc(b1 & lanes_lt);
+        const int step_flags = __popc(b0) + 2 * __popc(b1);
+        // slot of the cell that ENDS at the lane's k-th cell start (= the previous cell); the
+        // task's very first cell start ends nothing.  Loaded now, used after the reduction.
+        const int rb   = rank + excl - 1;
+        const int skip = (rb < 0) ? 1 : 0;
+        int s0 = 0, s1 = 0, s2 = 0;
+        if (cnt > skip) s0 = __ldg(pp + rb + skip);      // first cell start that stores
+        if (cnt > 1 + skip) s1 = __ldg(pp + rb + 1 + skip);
+        if (cnt > 2 + skip) s2 = __ldg(pp + rb + 2 + skip);
+        // sequential segmented sum inside the lane; c0/c1/c2 = the sums closed at the lane's
+        // first / second / third cell start (cell starts are >= 3 apart)
+        RT c0 = RT(0), c1 = RT(0), c2 = RT(0);
         RT run = RT(0);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          closev[i] = run;
-          if (fmask & (1u << i)) run = RT(0);
+          if (fmask & (1u << i)) {
+            const uint32_t below = fmask & ((1u << i) - 1u);
+            if (i < 3) {
+              c0 = run;
+            } else if (i < 6) {
+              if (below == 0) c0 = run; else c1 = run;
+            } else {
+              const int nb = __popc(below);
+              if (nb == 0) c0 = run; else if (nb == 1) c1 = run; else c2 = run;
+            }
+            run = RT(0);
+          }
           run += v[i];
         }
-        // segmented inclusive scan of the open tails across the lanes
-        RT sv      = run;
-        bool sflag = cnt > 0;
+        // segmented inclusive scan of the open tails across the lanes: lane l adds the tails of
+        // the lanes back to the nearest lane that holds a cell start
+        const uint32_t fl = __ballot_sync(0xffffffffu, cnt > 0);
+        const uint32_t le = fl & (lanes_lt | (1u << lane));
+        const int seg0    = le ? 31 - __clz(le) : 0;   // first lane of this lane's segment
+        RT sv = run;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-          const RT pv   = __shfl_up_sync(0xffffffffu, sv, o);
-          const int pf  = __shfl_up_sync(0xffffffffu, sflag ? 1 : 0, o);
-          if (lane >= o) {
-            if (!sflag) sv += pv;
-            sflag = sflag || (pf != 0);
-          }
+          const RT pv = __shfl_up_sync(0xffffffffu, sv, o);
+          if (lane - o >= seg0) sv += pv;
         }
         // what is open when the lane's first edge is reached
-        RT up_v        = __shfl_up_sync(0xffffffffu, sv, 1);
-        const int up_f = __shfl_up_sync(0xffffffffu, sflag ? 1 : 0, 1);
-        RT carry_in    = carry;
-        if (lane > 0) carry_in = up_f ? up_v : up_v + carry;
-        const RT last_v   = __shfl_sync(0xffffffffu, sv, 31);
-        const int last_f  = __shfl_sync(0xffffffffu, sflag ? 1 : 0, 31);
-        // stores: the first cell start of the lane closes the cell carried into the lane
-        bool first = true;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          if (fmask & (1u << i)) {
-            const RT val = first ? closev[i] + carry_in : closev[i];
-            first        = false;
-            if (slot[i] >= 0) pval[slot[i]] = val;
+        const RT up_v = __shfl_up_sync(0xffffffffu, sv, 1);
+        RT carry_in   = carry;
+        if (lane > 0) carry_in = (fl & lanes_lt) ? up_v : up_v + carry;
+        const RT last_v = __shfl_sync(0xffffffffu, sv, 31);
+        // stores
+        if (cnt > 0) {
+          c0 += carry_in;   // the lane's first cell start closes the cell carried into the lane
+          if (skip) {       // ... unless it is the task's first cell start
+            if (cnt > 1) pval[s0] = c1;
+            if (cnt > 2) pval[s1] = c2;
+          } else {
+            pval[s0] = c0;
+            if (cnt > 1) pval[s1] = c1;
+            if (cnt > 2) pval[s2] = c2;
           }
         }
-        carry = last_f ? last_v : last_v + carry;
+        carry = fl ? last_v : last_v + carry;
         rank += step_flags;
         cur = nxt;
       }
       // the cell that is still open at the end of the task
-      if (lane == 0 && rank > t.rank_first) pval[__ldg(P.ppos + rank - 1)] = carry;
+      if (lane == 0 && rank > 0) pval[__ldg(pp + rank - 1)] = carry;
     }
   }
 }

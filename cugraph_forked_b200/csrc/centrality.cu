@@ -141,6 +141,8 @@ struct pull_launcher {
   edge_partition* kp{nullptr};   // the partition the tiled kernel walks (ep or the reduced one)
   dbuf<RT> pval;
   const RT* kweights{nullptr};   // weights of kp
+  dbuf<int32_t> band_queue;      // two unit counters of phase 1, used alternately
+  int64_t band_launches{0};
 
   void init(b200_handle* h_, b200_graph* g, edge_partition* ep_);
 
@@ -220,6 +222,9 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
       kp       = bl->reduced.get();
       kweights = weighted ? reinterpret_cast<const RT*>(kp->weights.data()) : nullptr;
       pval.alloc(static_cast<size_t>(bl->num_partials), s, 8);
+      band_queue.alloc(2, s);
+      CUDA_TRY(cudaMemsetAsync(band_queue.data(), 0, 8, s));
+      band_launches = 0;
       static bool configured = false;
       if (!configured) {
         CUDA_TRY(cudaFuncSetAttribute(band_reduce_kernel<RT, true>,
@@ -291,7 +296,10 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
     B.ppos            = banded->ppos.data();
     B.tasks           = banded->tasks.data();
     B.groups          = banded->groups.data();
-    B.cta_group_first = banded->cta_group_first.data();
+    B.num_groups      = static_cast<int32_t>(banded->num_groups);
+    B.queue           = band_queue.data() + (band_launches & 1);
+    B.queue_next      = band_queue.data() + ((band_launches + 1) & 1);
+    ++band_launches;
     B.num_minors      = ep->num_minors;
     B.state           = state;
     const size_t smem = static_cast<size_t>(band_geom<RT>::entries) * sizeof(RT);

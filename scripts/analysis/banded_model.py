@@ -84,7 +84,8 @@ def build_layout(off, idx, w, num_minors, bits, minc=3, cellmax=2048, window=204
 
 
 def run_task(L, t, x, pval, dtype):
-    """band_reduce_kernel, one task on one warp: 32 lanes x 8 edges per step."""
+    """band_reduce_kernel, one task on one warp: 32 lanes x 8 edges per step (the same
+    statements as the CUDA kernel, including the 3-cell-starts-per-lane bound)."""
     bits = L["bits"]
     mask = (1 << bits) - 1
     bidx, bw, ppos = L["bidx"], L["bw"], L["ppos"]
@@ -93,80 +94,98 @@ def run_task(L, t, x, pval, dtype):
     lead = t["first"] - a0
     total = lead + t["count"]
     steps = (total + 255) // 256
-    rank = t["rank_first"]
+    pp = t["rank_first"]
+    rank = 0
     carry = dtype(0)
+
+    def store(slot, val):
+        assert np.isnan(pval[slot]), "partial written twice"
+        pval[slot] = val
+
     for st in range(steps):
-        fm = [0] * 32; vm = [0] * 32
-        h = [[0] * 8 for _ in range(32)]
+        cnt = [0] * 32; fm = [0] * 32
+        vals = [[dtype(0)] * 8 for _ in range(32)]
         for lane in range(32):
             base = st * 256 + lane * 8
             for i in range(8):
                 pos = a0 + base + i
                 hv = int(bidx[pos]) if pos < bidx.size else 0
-                h[lane][i] = hv
                 valid = lead <= base + i < total
                 if valid:
-                    vm[lane] |= 1 << i
+                    v = dtype(x[band0 + (hv & mask)])
+                    if bw is not None:
+                        v = dtype(v * bw[pos])
+                    vals[lane][i] = v
                     if hv & 0x8000:
                         fm[lane] |= 1 << i
-        cnt = [bin(m).count("1") for m in fm]
-        incl = np.cumsum(cnt)
-        excl = incl - cnt
-        step_flags = int(incl[31])
+            cnt[lane] = bin(fm[lane]).count("1")
+            assert cnt[lane] <= 3, "more than 3 cell starts in a lane"
+        b0 = sum(((cnt[l] & 1) != 0) << l for l in range(32))
+        b1 = sum(((cnt[l] & 2) != 0) << l for l in range(32))
+        popc = lambda m: bin(m).count("1")
+        step_flags = popc(b0) + 2 * popc(b1)
+        fl = sum((cnt[l] > 0) << l for l in range(32))
         run_tail = [dtype(0)] * 32
-        closev = [[dtype(0)] * 8 for _ in range(32)]
-        slot = [[-1] * 8 for _ in range(32)]
+        caps = [None] * 32
+        slots = [None] * 32
         for lane in range(32):
-            base = st * 256 + lane * 8
-            for i in range(8):
-                if fm[lane] & (1 << i):
-                    r = rank + excl[lane] + bin(fm[lane] & ((1 << i) - 1)).count("1") - 1
-                    if r >= t["rank_first"]:
-                        slot[lane][i] = int(ppos[r])
+            lt = (1 << lane) - 1
+            excl = popc(b0 & lt) + 2 * popc(b1 & lt)
+            rb = rank + excl - 1
+            skip = 1 if rb < 0 else 0
+            s = [0, 0, 0]
+            if cnt[lane] > skip: s[0] = int(ppos[pp + rb + skip])
+            if cnt[lane] > 1 + skip: s[1] = int(ppos[pp + rb + 1 + skip])
+            if cnt[lane] > 2 + skip: s[2] = int(ppos[pp + rb + 2 + skip])
+            slots[lane] = (s, skip)
+            c = [dtype(0)] * 3
             run = dtype(0)
             for i in range(8):
-                v = dtype(0)
-                if vm[lane] & (1 << i):
-                    v = dtype(x[band0 + (h[lane][i] & mask)])
-                    if bw is not None:
-                        v = dtype(v * bw[a0 + base + i])
-                closev[lane][i] = run
                 if fm[lane] & (1 << i):
+                    below = fm[lane] & ((1 << i) - 1)
+                    if i < 3:
+                        c[0] = run
+                    elif i < 6:
+                        if below == 0: c[0] = run
+                        else: c[1] = run
+                    else:
+                        c[popc(below)] = run
                     run = dtype(0)
-                run = dtype(run + v)
+                run = dtype(run + vals[lane][i])
+            caps[lane] = c
             run_tail[lane] = run
-        # segmented inclusive scan (Hillis-Steele, exactly the shuffle sequence)
         sv = list(run_tail)
-        sf = [c > 0 for c in cnt]
+        seg0 = []
+        for lane in range(32):
+            le = fl & ((1 << (lane + 1)) - 1)
+            seg0.append(le.bit_length() - 1 if le else 0)
         o = 1
         while o < 32:
             pv = [sv[l - o] if l >= o else dtype(0) for l in range(32)]
-            pf = [sf[l - o] if l >= o else False for l in range(32)]
             for l in range(32):
-                if l >= o:
-                    if not sf[l]:
-                        sv[l] = dtype(sv[l] + pv[l])
-                    sf[l] = sf[l] or pf[l]
+                if l - o >= seg0[l]:
+                    sv[l] = dtype(sv[l] + pv[l])
             o <<= 1
         for lane in range(32):
-            if lane == 0:
-                carry_in = carry
-            else:
-                carry_in = sv[lane - 1] if sf[lane - 1] else dtype(sv[lane - 1] + carry)
-            first = True
-            for i in range(8):
-                if fm[lane] & (1 << i):
-                    val = dtype(closev[lane][i] + carry_in) if first else closev[lane][i]
-                    first = False
-                    if slot[lane][i] >= 0:
-                        assert np.isnan(pval[slot[lane][i]]), "partial written twice"
-                        pval[slot[lane][i]] = val
-        carry = sv[31] if sf[31] else dtype(sv[31] + carry)
+            lt = (1 << lane) - 1
+            carry_in = carry
+            if lane > 0:
+                carry_in = sv[lane - 1] if (fl & lt) else dtype(sv[lane - 1] + carry)
+            if cnt[lane] > 0:
+                c = caps[lane]
+                s, skip = slots[lane]
+                c0 = dtype(c[0] + carry_in)
+                if skip:
+                    if cnt[lane] > 1: store(s[0], c[1])
+                    if cnt[lane] > 2: store(s[1], c[2])
+                else:
+                    store(s[0], c0)
+                    if cnt[lane] > 1: store(s[1], c[1])
+                    if cnt[lane] > 2: store(s[2], c[2])
+        carry = sv[31] if fl else dtype(sv[31] + carry)
         rank += step_flags
-    if rank > t["rank_first"]:
-        s = int(ppos[rank - 1])
-        assert np.isnan(pval[s]), "partial written twice"
-        pval[s] = carry
+    if rank > 0:
+        store(int(ppos[pp + rank - 1]), carry)
 
 
 def spmv_banded(L, x, dtype=np.float64):

@@ -26,7 +26,7 @@ def _csc(scale, ef, seed):
 @pytest.mark.parametrize("bits,cellmax,window,minc,hot_min,weighted", [
     (6, 64, 64, 3, 16, False),
     (6, 32, 64, 3, 1, True),
-    (4, 16, 16, 2, 8, True),
+    (4, 16, 16, 3, 8, True),
     (8, 2048, 2048, 3, 64, False),
     (5, 24, 40, 4, 1, False),
 ])
