@@ -64,10 +64,18 @@ __global__ void mark_cell_starts_kernel(const int32_t* idx, int64_t ne, int bits
   }
 }
 
-// c8[e] = 1 if the cell of edge e has >= kMinCell edges; hist[band] += 1 for those edges
-__global__ void classify_kernel(const uint8_t* f8, const int32_t* idx, int64_t ne, int bits,
+// c8[e] = 1 if the cell of edge e has >= kMinCell edges; hist[band] += 1 for those edges.
+// The histogram is kept per block in shared memory (nb <= kMaxBands bins); inside a warp the
+// 32 consecutive edges form a few runs of equal band (neighbour lists ascend), and only the
+// first lane of a run adds the run's candidate count.
+constexpr int kMaxBands = 8192;
+
+__global__ void classify_kernel(const uint8_t* f8, const int32_t* idx, int64_t ne, int bits, int nb,
                                 uint8_t* c8, unsigned long long* hist)
 {
+  extern __shared__ uint32_t s_hist[];
+  for (int k = threadIdx.x; k < nb; k += blockDim.x) s_hist[k] = 0;
+  __syncthreads();
   const int lane = threadIdx.x & 31;
   const int64_t stride = int64_t(gridDim.x) * blockDim.x;
   const int64_t rounds = (ne + stride - 1) / stride;
@@ -76,16 +84,15 @@ __global__ void classify_kernel(const uint8_t* f8, const int32_t* idx, int64_t n
     bool cand = false;
     int band  = -1;
     if (e < ne) {
+      band = idx[e] >> bits;
       // nearest cell start at or before e, within kMinCell - 1 edges
       int64_t p = -1;
 #pragma unroll
       for (int j = 0; j < kMinCell; ++j) {
         if (p < 0 && e - j >= 0 && (f8[e - j] & 2u)) p = e - j;
       }
-      if (p < 0) {
-        cand = true;  // the cell started >= kMinCell edges ago
-      } else {
-        cand = true;
+      cand = true;  // no start found: the cell started >= kMinCell edges ago
+      if (p >= 0) {
 #pragma unroll
         for (int j = 1; j < kMinCell; ++j) {
           const int64_t q = p + j;
@@ -93,13 +100,23 @@ __global__ void classify_kernel(const uint8_t* f8, const int32_t* idx, int64_t n
         }
       }
       c8[e] = cand ? 1 : 0;
-      if (cand) band = idx[e] >> bits;
     }
-    // warp-aggregated histogram
-    const unsigned peers = __match_any_sync(0xffffffffu, band);
-    if (band >= 0 && lane == __ffs(peers) - 1)
-      atomicAdd(hist + band, static_cast<unsigned long long>(__popc(peers)));
+    // runs of equal band inside the warp
+    const int prev       = __shfl_up_sync(0xffffffffu, band, 1);
+    const bool head      = lane == 0 || prev != band;
+    const uint32_t heads = __ballot_sync(0xffffffffu, head);
+    const uint32_t cands = __ballot_sync(0xffffffffu, cand);
+    if (head && band >= 0) {
+      const uint32_t above = heads & ~((2u << lane) - 1u);          // heads after this lane
+      const int end        = above ? __ffs(above) - 1 : 32;         // first lane of the next run
+      const uint32_t run   = (end >= 32 ? 0xffffffffu : ((1u << end) - 1u)) & ~((1u << lane) - 1u);
+      const int n          = __popc(cands & run);
+      if (n) atomicAdd(&s_hist[band], static_cast<uint32_t>(n));
+    }
   }
+  __syncthreads();
+  for (int k = threadIdx.x; k < nb; k += blockDim.x)
+    if (s_hist[k]) atomicAdd(hist + k, static_cast<unsigned long long>(s_hist[k]));
 }
 
 __global__ void mark_hot_kernel(const unsigned long long* hist, int nb, long long min_edges,
@@ -241,7 +258,8 @@ static void build_banded(b200_handle* h, edge_partition& ep, const RT* w, banded
   L.band_bits      = bits;
   L.value_size     = static_cast<int>(sizeof(RT));
   L.enabled        = false;
-  if (ne < (int64_t{1} << 16) || ne >= (int64_t{1} << 31) - 4096 || nb <= 0 || ep.offsets64 ||
+  if (ne < (int64_t{1} << 16) || ne >= (int64_t{1} << 31) - 4096 || nb <= 0 || nb > kMaxBands ||
+      ep.offsets64 ||
       !ep.has_segments || ep.generic_schedule)
     return;
   CUDA_TRY(cudaStreamSynchronize(s));
@@ -259,7 +277,8 @@ static void build_banded(b200_handle* h, edge_partition& ep, const RT* w, banded
   mark_cell_starts_kernel<<<bgrid(n), kBT, 0, s>>>(idx, ne, bits, f8.data());
   {
     dbuf<uint8_t> c8(n + 8, s);
-    classify_kernel<<<bgrid(n), kBT, 0, s>>>(f8.data(), idx, ne, bits, c8.data(), hist.data());
+    classify_kernel<<<bgrid(n), kBT, static_cast<size_t>(nb) * 4, s>>>(f8.data(), idx, ne, bits, nb,
+                                                                       c8.data(), hist.data());
     const char* env = std::getenv("B200_BAND_HOT_MIN");
     const long long hot_min = env ? std::atoll(env) : kHotBandMin;
     mark_hot_kernel<<<bgrid(static_cast<size_t>(nb)), kBT, 0, s>>>(hist.data(), nb, hot_min,

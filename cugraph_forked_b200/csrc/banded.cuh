@@ -30,7 +30,11 @@ namespace b200 {
 
 constexpr int kBandThreads = 1024;
 constexpr int kBandWarps   = kBandThreads / 32;
-constexpr int kMinCell     = 3;      // cells with fewer edges stay direct gathers
+#ifndef B200_MIN_CELL
+#define B200_MIN_CELL 3
+#endif
+constexpr int kMinCell     = B200_MIN_CELL;  // cells with fewer edges stay direct gathers
+constexpr int kLaneFlags   = (8 + kMinCell - 1) / kMinCell;  // most cell starts in 8 edges
 constexpr int kCellMax     = 2048;   // cells are cut at CSC positions that are multiples of this
 constexpr int kTaskWindow  = 2048;   // a task = the cells that start inside one window of a band
 constexpr int kStepEdges   = 256;    // edges a warp handles per step (8 per lane, one LDG.128)
@@ -122,7 +126,7 @@ template <typename RT, bool WEIGHTED>
 __global__ void __launch_bounds__(kBandThreads, 1) band_reduce_kernel(const __grid_constant__ band_params P)
 {
   using G = band_geom<RT>;
-  static_assert(kMinCell >= 3, "a lane of 8 consecutive edges must hold at most 3 cell starts");
+  static_assert(kMinCell >= 2 && kLaneFlags <= 4, "a lane of 8 edges holds at most 4 cell starts");
   extern __shared__ __align__(16) unsigned char band_smem[];
   RT* band = reinterpret_cast<RT*>(band_smem);
   __shared__ int s_next;
@@ -216,36 +220,44 @@ __global__ void __launch_bounds__(kBandThreads, 1) band_reduce_kernel(const __gr
           for (int i = 0; i < 8; ++i)
             if (!(vmask & (1u << i))) v[i] = RT(0);
         }
-        // ranks of the lane's cell starts: cells have >= kMinCell = 3 edges, so a lane holds at
-        // most 3 of them and two ballots give the exclusive prefix of the counts
-        const int cnt        = __popc(fmask);
-        const uint32_t b0    = __ballot_sync(0xffffffffu, cnt & 1);
-        const uint32_t b1    = __ballot_sync(0xffffffffu, cnt & 2);
-        const int excl       = __popc(b0 & lanes_lt) + 2 * __popc(b1 & lanes_lt);
-        const int step_flags = __popc(b0) + 2 * __popc(b1);
+        // ranks of the lane's cell starts: cells have >= kMinCell edges, so a lane holds at most
+        // kLaneFlags of them and 2-3 ballots give the exclusive prefix of the counts
+        const int cnt     = __popc(fmask);
+        const uint32_t b0 = __ballot_sync(0xffffffffu, cnt & 1);
+        const uint32_t b1 = __ballot_sync(0xffffffffu, cnt & 2);
+        int excl          = __popc(b0 & lanes_lt) + 2 * __popc(b1 & lanes_lt);
+        int step_flags    = __popc(b0) + 2 * __popc(b1);
+        if constexpr (kLaneFlags > 3) {
+          const uint32_t b2 = __ballot_sync(0xffffffffu, cnt & 4);
+          excl += 4 * __popc(b2 & lanes_lt);
+          step_flags += 4 * __popc(b2);
+        }
         // slot of the cell that ENDS at the lane's k-th cell start (= the previous cell); the
         // task's very first cell start ends nothing.  Loaded now, used after the reduction.
         const int rb   = rank + excl - 1;
         const int skip = (rb < 0) ? 1 : 0;
-        int s0 = 0, s1 = 0, s2 = 0;
-        if (cnt > skip) s0 = __ldg(pp + rb + skip);      // first cell start that stores
-        if (cnt > 1 + skip) s1 = __ldg(pp + rb + 1 + skip);
-        if (cnt > 2 + skip) s2 = __ldg(pp + rb + 2 + skip);
-        // sequential segmented sum inside the lane; c0/c1/c2 = the sums closed at the lane's
-        // first / second / third cell start (cell starts are >= 3 apart)
-        RT c0 = RT(0), c1 = RT(0), c2 = RT(0);
+        int sl[kLaneFlags];
+#pragma unroll
+        for (int k = 0; k < kLaneFlags; ++k) {
+          sl[k] = 0;
+          if (cnt > k + skip) sl[k] = __ldg(pp + rb + k + skip);   // k-th cell start that stores
+        }
+        // sequential segmented sum inside the lane; c[k] = the sum closed at the lane's k-th cell
+        // start (cell starts are >= kMinCell apart, so start k sits at position >= k * kMinCell)
+        RT c[kLaneFlags];
+#pragma unroll
+        for (int k = 0; k < kLaneFlags; ++k) c[k] = RT(0);
         RT run = RT(0);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           if (fmask & (1u << i)) {
-            const uint32_t below = fmask & ((1u << i) - 1u);
-            if (i < 3) {
-              c0 = run;
-            } else if (i < 6) {
-              if (below == 0) c0 = run; else c1 = run;
+            if (i < kMinCell) {
+              c[0] = run;
             } else {
-              const int nb = __popc(below);
-              if (nb == 0) c0 = run; else if (nb == 1) c1 = run; else c2 = run;
+              const int nb = __popc(fmask & ((1u << i) - 1u));
+#pragma unroll
+              for (int k = 0; k < kLaneFlags; ++k)
+                if (k * kMinCell <= i && nb == k) c[k] = run;
             }
             run = RT(0);
           }
@@ -267,17 +279,17 @@ __global__ void __launch_bounds__(kBandThreads, 1) band_reduce_kernel(const __gr
         RT carry_in   = carry;
         if (lane > 0) carry_in = (fl & lanes_lt) ? up_v : up_v + carry;
         const RT last_v = __shfl_sync(0xffffffffu, sv, 31);
-        // stores
+        // stores: the lane's first cell start closes the cell carried into the lane, unless it
+        // is the task's first cell start
         if (cnt > 0) {
-          c0 += carry_in;   // the lane's first cell start closes the cell carried into the lane
-          if (skip) {       // ... unless it is the task's first cell start
-            if (cnt > 1) pval[s0] = c1;
-            if (cnt > 2) pval[s1] = c2;
-          } else {
-            pval[s0] = c0;
-            if (cnt > 1) pval[s1] = c1;
-            if (cnt > 2) pval[s2] = c2;
+          c[0] += carry_in;
+          if (skip) {
+#pragma unroll
+            for (int k = 0; k + 1 < kLaneFlags; ++k) c[k] = c[k + 1];
           }
+#pragma unroll
+          for (int k = 0; k < kLaneFlags; ++k)
+            if (cnt > k + skip) pval[sl[k]] = c[k];
         }
         carry = fl ? last_v : last_v + carry;
         rank += step_flags;

@@ -53,6 +53,24 @@ template <>
 struct default_cfg<double, true> {
   using type = pull_cfg<1024, 4, 256>;
 };
+// phase 2 of the banded path walks the reduced partition: a quarter of the entries on the same
+// rows, so tiles are row-limited and a larger row cap pays (profiles/r1e_sweep_*.log)
+template <typename RT, bool WEIGHTED>
+struct banded_cfg {
+  using type = pull_cfg<4096, 4, 1024>;  // f32 unweighted
+};
+template <>
+struct banded_cfg<float, true> {
+  using type = pull_cfg<2048, 4, 1024>;
+};
+template <>
+struct banded_cfg<double, false> {
+  using type = pull_cfg<2048, 4, 512>;   // a larger row cap measured slower (r1g_quick_*.log)
+};
+template <>
+struct banded_cfg<double, true> {
+  using type = pull_cfg<1024, 4, 256>;
+};
 // alternatives for tuning sweeps (B200_PULL_CFG=1..), f32 unweighted int32 offsets only
 template <int ID>
 struct alt_cfg {
@@ -63,10 +81,16 @@ template <> struct alt_cfg<2> { using type = pull_cfg<4096, 4, 1024>; };
 template <> struct alt_cfg<3> { using type = pull_cfg<4096, 3, 512>; };
 template <> struct alt_cfg<4> { using type = pull_cfg<4096, 5, 512>; };
 template <> struct alt_cfg<5> { using type = pull_cfg<8192, 2, 1024>; };
-constexpr int kNumAltCfg = 6;
+template <> struct alt_cfg<6> { using type = pull_cfg<4096, 3, 2048>; };
+template <> struct alt_cfg<7> { using type = pull_cfg<4096, 4, 2048>; };
+template <> struct alt_cfg<8> { using type = pull_cfg<8192, 3, 2048>; };
+template <> struct alt_cfg<9> { using type = pull_cfg<2048, 6, 1024>; };
+template <> struct alt_cfg<10> { using type = pull_cfg<4096, 5, 1024>; };
+constexpr int kNumAltCfg = 11;
 
-// the two-phase banded path (banded.cuh) is opt-in until measured: B200_BANDED=1
-constexpr int kBandedDefault = 0;
+// the two-phase banded path (banded.cuh) is the single-GPU default (measured 1.8x the tiled
+// kernel alone at scale 24, profiles/r1d_*); B200_BANDED=0 selects the single-phase kernel
+constexpr int kBandedDefault = 1;
 
 int env_int(const char* name, int dflt)
 {
@@ -134,6 +158,7 @@ struct pull_launcher {
   int rowcap{0};
   int cfg_id{0};
   bool tiled{false};
+  bool banded_tiles{false};      // phase 2 uses banded_cfg instead of default_cfg
   int64_t launches{0};
   // two-phase path (banded.cuh): phase 1 pre-reduces the cells of the hot bands from shared
   // memory into `pval`, phase 2 runs the tiled kernel over the reduced partition `kp`
@@ -204,18 +229,35 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
   if (sizeof(RT) == 4 && !weighted && !ep->offsets64) {
     cfg_id = std::max(0, std::min(kNumAltCfg - 1, env_int("B200_PULL_CFG", 0)));
     const int ts[kNumAltCfg] = {alt_cfg<0>::type::T, alt_cfg<1>::type::T, alt_cfg<2>::type::T,
-                                alt_cfg<3>::type::T, alt_cfg<4>::type::T, alt_cfg<5>::type::T};
+                                alt_cfg<3>::type::T, alt_cfg<4>::type::T, alt_cfg<5>::type::T,
+                                alt_cfg<6>::type::T, alt_cfg<7>::type::T, alt_cfg<8>::type::T,
+                                alt_cfg<9>::type::T, alt_cfg<10>::type::T};
     const int rs[kNumAltCfg] = {alt_cfg<0>::type::ROWCAP, alt_cfg<1>::type::ROWCAP,
                                 alt_cfg<2>::type::ROWCAP, alt_cfg<3>::type::ROWCAP,
-                                alt_cfg<4>::type::ROWCAP, alt_cfg<5>::type::ROWCAP};
+                                alt_cfg<4>::type::ROWCAP, alt_cfg<5>::type::ROWCAP,
+                                alt_cfg<6>::type::ROWCAP, alt_cfg<7>::type::ROWCAP,
+                                alt_cfg<8>::type::ROWCAP, alt_cfg<9>::type::ROWCAP,
+                                alt_cfg<10>::type::ROWCAP};
     T      = ts[cfg_id];
     rowcap = rs[cfg_id];
   }
   kp       = ep;
   kweights = weights;
   banded   = nullptr;
+  banded_tiles = false;
   if (tiled && !g->multi_gpu && !ep->generic_schedule && !ep->offsets64 &&
       env_int("B200_BANDED", kBandedDefault) != 0) {
+    const int T0 = T, rowcap0 = rowcap;
+    if (cfg_id == 0 && env_int("B200_BANDED_CFG", 1) != 0) {
+      banded_tiles = true;
+      if (weighted) {
+        T      = banded_cfg<RT, true>::type::T;
+        rowcap = banded_cfg<RT, true>::type::ROWCAP;
+      } else {
+        T      = banded_cfg<RT, false>::type::T;
+        rowcap = banded_cfg<RT, false>::type::ROWCAP;
+      }
+    }
     banded_layout* bl = banded_get<RT>(h, *ep, weights, T, rowcap);
     if (bl && bl->enabled) {
       banded   = bl;
@@ -235,6 +277,10 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
                                       band_geom<RT>::entries * static_cast<int>(sizeof(RT))));
         configured = true;
       }
+    } else {
+      banded_tiles = false;
+      T            = T0;
+      rowcap       = rowcap0;
     }
   }
   if (tiled) {
@@ -335,6 +381,7 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
     constexpr bool W = decltype(wtag)::value;
     using CFG        = typename decltype(cfgtag)::type;
     using SM         = pull_smem<ET, RT, W, CFG::T, CFG::STAGES, CFG::ROWCAP, EPI::kStage>;
+    static_assert(SM::ring <= SM::max_dyn, "tile configuration exceeds the shared memory of an SM");
     auto kern        = pull_tiles_kernel<ET, RT, W, EPI, CFG::T, CFG::STAGES, CFG::ROWCAP>;
     // the hub cache takes what is left of the shared-memory budget; the budget leaves L1 enough
     // lines to track the outstanding gathers (profiles/microbench_gather.md)
@@ -342,6 +389,9 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
     int64_t room = std::max<int64_t>(0, budget - static_cast<int64_t>(SM::ring)) / sizeof(RT);
     int hub = static_cast<int>(std::min<int64_t>({kp->num_minors, SM::max_hub, room})) & ~31;
     hub     = std::max(0, std::min(hub, hub_cap));
+    // the entries phase 2 still gathers from x are spread over millions of sources (5 % hit a
+    // 16 K cache): no hub cache, the shared memory goes to L1 instead
+    if (banded && env_int("B200_BANDED_HUB", 0) == 0) hub = 0;
     static bool configured = false;
     if (!configured) {
       CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -374,10 +424,16 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
         case 3: launch(et, wtag, alt_cfg<3>{}); return;
         case 4: launch(et, wtag, alt_cfg<4>{}); return;
         case 5: launch(et, wtag, alt_cfg<5>{}); return;
+        case 6: launch(et, wtag, alt_cfg<6>{}); return;
+        case 7: launch(et, wtag, alt_cfg<7>{}); return;
+        case 8: launch(et, wtag, alt_cfg<8>{}); return;
+        case 9: launch(et, wtag, alt_cfg<9>{}); return;
+        case 10: launch(et, wtag, alt_cfg<10>{}); return;
         default: break;
       }
     }
-    launch(et, wtag, default_cfg<RT, W>{});
+    if (banded_tiles) launch(et, wtag, banded_cfg<RT, W>{});
+    else launch(et, wtag, default_cfg<RT, W>{});
   };
   if (kp->offsets64) {
     if (weighted) go(int64_t{}, std::true_type{}); else go(int64_t{}, std::false_type{});

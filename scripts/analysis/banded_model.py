@@ -83,7 +83,7 @@ def build_layout(off, idx, w, num_minors, bits, minc=3, cellmax=2048, window=204
                 nb=nb)
 
 
-def run_task(L, t, x, pval, dtype):
+def run_task(L, t, x, pval, dtype, minc=3):
     """band_reduce_kernel, one task on one warp: 32 lanes x 8 edges per step (the same
     statements as the CUDA kernel, including the 3-cell-starts-per-lane bound)."""
     bits = L["bits"]
@@ -95,6 +95,7 @@ def run_task(L, t, x, pval, dtype):
     total = lead + t["count"]
     steps = (total + 255) // 256
     pp = t["rank_first"]
+    lane_flags = (8 + minc - 1) // minc
     rank = 0
     carry = dtype(0)
 
@@ -119,37 +120,31 @@ def run_task(L, t, x, pval, dtype):
                     if hv & 0x8000:
                         fm[lane] |= 1 << i
             cnt[lane] = bin(fm[lane]).count("1")
-            assert cnt[lane] <= 3, "more than 3 cell starts in a lane"
-        b0 = sum(((cnt[l] & 1) != 0) << l for l in range(32))
-        b1 = sum(((cnt[l] & 2) != 0) << l for l in range(32))
+            assert cnt[lane] <= lane_flags, "too many cell starts in a lane"
         popc = lambda m: bin(m).count("1")
-        step_flags = popc(b0) + 2 * popc(b1)
+        step_flags = sum(cnt)
         fl = sum((cnt[l] > 0) << l for l in range(32))
         run_tail = [dtype(0)] * 32
         caps = [None] * 32
         slots = [None] * 32
         for lane in range(32):
-            lt = (1 << lane) - 1
-            excl = popc(b0 & lt) + 2 * popc(b1 & lt)
+            excl = sum(cnt[:lane])
             rb = rank + excl - 1
             skip = 1 if rb < 0 else 0
-            s = [0, 0, 0]
-            if cnt[lane] > skip: s[0] = int(ppos[pp + rb + skip])
-            if cnt[lane] > 1 + skip: s[1] = int(ppos[pp + rb + 1 + skip])
-            if cnt[lane] > 2 + skip: s[2] = int(ppos[pp + rb + 2 + skip])
+            s = [0] * lane_flags
+            for k in range(lane_flags):
+                if cnt[lane] > k + skip: s[k] = int(ppos[pp + rb + k + skip])
             slots[lane] = (s, skip)
-            c = [dtype(0)] * 3
+            c = [dtype(0)] * lane_flags
             run = dtype(0)
             for i in range(8):
                 if fm[lane] & (1 << i):
-                    below = fm[lane] & ((1 << i) - 1)
-                    if i < 3:
+                    if i < minc:
                         c[0] = run
-                    elif i < 6:
-                        if below == 0: c[0] = run
-                        else: c[1] = run
                     else:
-                        c[popc(below)] = run
+                        nb = popc(fm[lane] & ((1 << i) - 1))
+                        for k in range(lane_flags):
+                            if k * minc <= i and nb == k: c[k] = run
                     run = dtype(0)
                 run = dtype(run + vals[lane][i])
             caps[lane] = c
@@ -174,24 +169,22 @@ def run_task(L, t, x, pval, dtype):
             if cnt[lane] > 0:
                 c = caps[lane]
                 s, skip = slots[lane]
-                c0 = dtype(c[0] + carry_in)
+                c = list(c)
+                c[0] = dtype(c[0] + carry_in)
                 if skip:
-                    if cnt[lane] > 1: store(s[0], c[1])
-                    if cnt[lane] > 2: store(s[1], c[2])
-                else:
-                    store(s[0], c0)
-                    if cnt[lane] > 1: store(s[1], c[1])
-                    if cnt[lane] > 2: store(s[2], c[2])
+                    c = c[1:] + [c[-1]]
+                for k in range(lane_flags):
+                    if cnt[lane] > k + skip: store(s[k], c[k])
         carry = sv[31] if fl else dtype(sv[31] + carry)
         rank += step_flags
     if rank > 0:
         store(int(ppos[pp + rank - 1]), carry)
 
 
-def spmv_banded(L, x, dtype=np.float64):
+def spmv_banded(L, x, dtype=np.float64, minc=3):
     pval = np.full(L["n_part"], np.nan, dtype)
     for t in L["tasks"]:
-        run_task(L, t, x, pval, dtype)
+        run_task(L, t, x, pval, dtype, minc)
     assert not np.isnan(pval).any(), "a partial was never written"
     xcat = np.concatenate([x.astype(dtype), pval])
     prod = xcat[L["ridx"]]

@@ -35,24 +35,17 @@ setenv(B200_BANDED=0)
 g = engine.Graph(h, s, d, vertices=verts)
 print("tiled           : %.4f ms/iter (spmv %.4f)" % run(g), flush=True)
 setenv(B200_BANDED=1)
-for hot in (32768, 8192, 131072, 524288):
-    setenv(B200_BAND_HOT_MIN=hot, B200_PULL_CFG=None, B200_SMEM_BUDGET_KB=None)
-    g = engine.Graph(h, s, d, vertices=verts)
-    print("banded hot_min=%7d : %.4f ms/iter (spmv %.4f)" % ((hot,) + run(g)), flush=True)
-setenv(B200_BAND_HOT_MIN=None)
 g = engine.Graph(h, s, d, vertices=verts)
 run(g)
 if dtype == torch.float32:
-    for cfg in (0, 1, 2, 3, 4, 5):
-        setenv(B200_PULL_CFG=cfg)
-        print("banded cfg=%d      : %.4f ms/iter (spmv %.4f)" % ((cfg,) + run(g)), flush=True)
-    setenv(B200_PULL_CFG=None)
-for kb in (110, 130, 160, 190, 210):
-    setenv(B200_SMEM_BUDGET_KB=kb)
-    print("banded smem=%3d KB : %.4f ms/iter (spmv %.4f)" % ((kb,) + run(g)), flush=True)
-setenv(B200_SMEM_BUDGET_KB=None)
-for il in (0, 1):
-    setenv(B200_TILE_INTERLEAVE=il)
-    g2 = engine.Graph(h, s, d, vertices=verts)
-    print("banded interleave=%d: %.4f ms/iter (spmv %.4f)" % ((il,) + run(g2)), flush=True)
+    for hub in (None, 0):
+        for cfg in range(11):
+            setenv(B200_PULL_CFG=cfg, B200_HUB_ENTRIES=hub)
+            print("banded cfg=%2d hub=%-4s : %.4f ms/iter (spmv %.4f)" % ((cfg, hub) + run(g)), flush=True)
+    setenv(B200_PULL_CFG=None, B200_HUB_ENTRIES=None)
+else:
+    for hub in (None, 0, 2048):
+        setenv(B200_HUB_ENTRIES=hub)
+        print("banded hub=%-4s : %.4f ms/iter (spmv %.4f)" % ((hub,) + run(g)), flush=True)
+    setenv(B200_HUB_ENTRIES=None)
 print("SWEEP_OK")

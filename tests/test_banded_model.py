@@ -26,7 +26,8 @@ def _csc(scale, ef, seed):
 @pytest.mark.parametrize("bits,cellmax,window,minc,hot_min,weighted", [
     (6, 64, 64, 3, 16, False),
     (6, 32, 64, 3, 1, True),
-    (4, 16, 16, 3, 8, True),
+    (4, 16, 16, 2, 8, True),
+    (6, 64, 64, 2, 16, False),
     (8, 2048, 2048, 3, 64, False),
     (5, 24, 40, 4, 1, False),
 ])
@@ -43,7 +44,7 @@ def test_two_phase_equals_plain_spmv(bits, cellmax, window, minc, hot_min, weigh
     sizes = np.diff(np.append(starts, idx.size))
     true_cand = np.repeat(sizes >= minc, sizes)
     assert np.array_equal(true_cand, L["cand"])
-    y = bm.spmv_banded(L, x)
+    y = bm.spmv_banded(L, x, minc=minc)
     prod = x[idx] * (w if weighted else 1.0)
     ref = np.zeros(nv)
     nz = off[:-1] < off[1:]
