@@ -258,9 +258,10 @@ static void build_banded(b200_handle* h, edge_partition& ep, const RT* w, banded
   L.band_bits      = bits;
   L.value_size     = static_cast<int>(sizeof(RT));
   L.enabled        = false;
-  if (ne < (int64_t{1} << 16) || ne >= (int64_t{1} << 31) - 4096 || nb <= 0 || nb > kMaxBands ||
-      ep.offsets64 ||
-      !ep.has_segments || ep.generic_schedule)
+  const char* env_min   = std::getenv("B200_BAND_MIN_EDGES");
+  const int64_t min_edges = env_min ? std::atoll(env_min) : (int64_t{1} << 16);
+  if (ne < std::max<int64_t>(min_edges, 64) || ne >= (int64_t{1} << 31) - 4096 || nb <= 0 ||
+      nb > kMaxBands || ep.offsets64 || !ep.has_segments)
     return;
   CUDA_TRY(cudaStreamSynchronize(s));
   const auto t_begin = std::chrono::steady_clock::now();
@@ -325,6 +326,7 @@ static void build_banded(b200_handle* h, edge_partition& ep, const RT* w, banded
   for (int i = 0; i < 5; ++i) rp.seg[i] = ep.seg[i];
   rp.has_segments        = true;
   rp.generic_schedule    = true;   // long rows are listed by id (tail kernel)
+  L.generic_rows         = ep.generic_schedule;
   rp.minor_piece_offsets = {0, ep.num_minors};
 
   dbuf<uint64_t> k0(static_cast<size_t>(n_band), s), k1(static_cast<size_t>(n_band), s);
@@ -425,7 +427,8 @@ static void build_banded(b200_handle* h, edge_partition& ep, const RT* w, banded
   CUDA_TRY(cudaStreamSynchronize(s));
 
   // ---- phase-2 schedule -------------------------------------------------------------------
-  build_schedule_reduced(h, rp, ep.seg[1], ep.seg[3], tile_edges, row_cap);
+  if (L.generic_rows) build_schedule(h, rp, tile_edges, row_cap);
+  else build_schedule_reduced(h, rp, ep.seg[1], ep.seg[3], tile_edges, row_cap);
   L.enabled  = true;
   L.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin)
                  .count();
@@ -451,8 +454,10 @@ banded_layout* banded_get(b200_handle* h, edge_partition& ep, const RT* weights,
   } else if (ep.banded[slot]->enabled) {
     // the layout is cached per value width; the tile shape of phase 2 may differ between calls
     edge_partition& rp = *ep.banded[slot]->reduced;
-    if (rp.sched_tile_edges != tile_edges || rp.sched_row_cap != row_cap)
-      build_schedule_reduced(h, rp, ep.seg[1], ep.seg[3], tile_edges, row_cap);
+    if (rp.sched_tile_edges != tile_edges || rp.sched_row_cap != row_cap) {
+      if (ep.banded[slot]->generic_rows) build_schedule(h, rp, tile_edges, row_cap);
+      else build_schedule_reduced(h, rp, ep.seg[1], ep.seg[3], tile_edges, row_cap);
+    }
   }
   return ep.banded[slot].get();
 }

@@ -71,6 +71,9 @@ struct banded_layout {
   int band_bits{0};
   int value_size{0};
   bool enabled{false};          // false: the graph has too little to pre-reduce
+  // rows of a multi-GPU partition follow the GLOBAL degree order: the reduced partition is then
+  // scheduled by the generic host pass instead of build_schedule_reduced
+  bool generic_rows{false};
   int64_t num_banded_edges{0};
   int64_t num_partials{0};
   int64_t num_tasks{0};

@@ -245,8 +245,10 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
   kweights = weights;
   banded   = nullptr;
   banded_tiles = false;
-  if (tiled && !g->multi_gpu && !ep->generic_schedule && !ep->offsets64 &&
-      env_int("B200_BANDED", kBandedDefault) != 0) {
+  // multi-GPU: every edge partition gets its own layout (bands of its minor range); the
+  // opt-in fused rectangle keeps the single-phase kernel
+  const bool is_fused = !g->fused.empty() && ep == &g->fused[0];
+  if (tiled && !is_fused && !ep->offsets64 && env_int("B200_BANDED", kBandedDefault) != 0) {
     const int T0 = T, rowcap0 = rowcap;
     if (cfg_id == 0 && env_int("B200_BANDED_CFG", 1) != 0) {
       banded_tiles = true;
@@ -350,9 +352,9 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
     B.state           = state;
     const size_t smem = static_cast<size_t>(band_geom<RT>::entries) * sizeof(RT);
     if (weighted)
-      band_reduce_kernel<RT, true><<<banded->num_ctas, kBandThreads, smem, s>>>(B);
+      band_reduce_kernel<RT, true><<<main_ctas, kBandThreads, smem, s>>>(B);
     else
-      band_reduce_kernel<RT, false><<<banded->num_ctas, kBandThreads, smem, s>>>(B);
+      band_reduce_kernel<RT, false><<<main_ctas, kBandThreads, smem, s>>>(B);
     CUDA_TRY(cudaGetLastError());
     ++launches;
   }

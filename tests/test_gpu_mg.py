@@ -32,6 +32,18 @@ def test_mg_world_size_1(mg1, dtype, weighted):
     mg_worker.run(11, 16, dtype, weighted, mg1, 0, 1, verbose=False)
 
 
+@pytest.mark.parametrize("dtype,weighted", [(np.float32, True), (np.float64, False)])
+def test_mg_world_size_1_banded(mg1, monkeypatch, capfd, dtype, weighted):
+    """a partition large enough for the banded pre-reduction (banded.cu) on the MG code path:
+    generic schedule of the reduced partition, raw epilogue, exchange loop"""
+    from tests import mg_worker
+    monkeypatch.setenv("B200_BANDED", "1")
+    monkeypatch.setenv("B200_BAND_HOT_MIN", "1024")
+    monkeypatch.setenv("B200_BAND_VERBOSE", "1")
+    mg_worker.run(15, 16, dtype, weighted, mg1, 0, 1, verbose=False)
+    assert "banded layout" in capfd.readouterr().err
+
+
 def test_mg_tiny_graph_world_size_1(mg1):
     from tests import mg_worker
     mg_worker.run_tiny(mg1, 0, 1)
@@ -69,3 +81,10 @@ def test_mg_torchrun(world, oracle_built):
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=900)
     ok = r.stdout.count("MG_WORKER_OK")
     assert r.returncode == 0 and ok == 5 * world, (r.stdout[-3000:], r.stderr[-3000:])
+    # again with the banded pre-reduction forced onto the small partitions
+    env = dict(os.environ, B200_BANDED="1", B200_BAND_MIN_EDGES="512", B200_BAND_HOT_MIN="64",
+               B200_BAND_VERBOSE="1")
+    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=900, env=env)
+    ok = r.stdout.count("MG_WORKER_OK")
+    assert r.returncode == 0 and ok == 5 * world, (r.stdout[-3000:], r.stderr[-3000:])
+    assert "banded layout" in r.stderr
