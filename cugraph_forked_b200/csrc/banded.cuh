@@ -36,7 +36,11 @@ constexpr int kBandWarps   = kBandThreads / 32;
 constexpr int kMinCell     = B200_MIN_CELL;  // cells with fewer edges stay direct gathers
 constexpr int kLaneFlags   = (8 + kMinCell - 1) / kMinCell;  // most cell starts in 8 edges
 constexpr int kCellMax     = 2048;   // cells are cut at CSC positions that are multiples of this
-constexpr int kTaskWindow  = 2048;   // a task = the cells that start inside one window of a band
+#ifndef B200_TASK_WINDOW
+#define B200_TASK_WINDOW 4096
+#endif
+constexpr int kTaskWindow  = B200_TASK_WINDOW;  // a task = the cells that start inside one window of a band
+static_assert(kTaskWindow >= kCellMax, "every window must contain a cell start");
 constexpr int kStepEdges   = 256;    // edges a warp handles per step (8 per lane, one LDG.128)
 constexpr int64_t kBandLoadCost = 16384;  // cost of loading a band, in edges (CTA balancing)
 constexpr int64_t kHotBandMin   = 32768;  // bands with fewer pre-reducible edges stay direct
@@ -297,6 +301,193 @@ __global__ void __launch_bounds__(kBandThreads, 1) band_reduce_kernel(const __gr
         carry = fl ? last_v : last_v + carry;
         rank += step_flags;
         cur = nxt;
+      }
+      // the cell that is still open at the end of the task
+      if (lane == 0 && rank > 0) pval[__ldg(pp + rank - 1)] = carry;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// phase-1 kernel, second formulation (used for unweighted 4-byte values, where it measured 3 %
+// faster; the first formulation is faster for the other types): LE = 16 (4-byte values) or 8
+// (8-byte values) edges per lane and step, and the per-position running sums go through a
+// private column of a shared-memory scratch array instead of registers, so that the cells that
+// end in a lane are handled by a short loop over the lane's cell-start bits instead of
+// predicated code for every position.  Twice the edges per step halve the per-edge cost of the
+// ballots and of the segmented scan: 0.72 warp instructions per pre-reduced edge instead of
+// 1.0 - but the kernel then runs into the shared-memory pipe (76 % busy: the random band
+// gathers cost 5.3 wavefronts each), profiles/r1l_ncu_band_reduce2.md.
+// ------------------------------------------------------------------------------------------
+template <typename RT>
+struct band_geom2 {
+  static constexpr int LE         = sizeof(RT) == 4 ? 16 : 8;   // edges per lane and step
+  static constexpr int step_edges = 32 * LE;
+  static constexpr size_t smem    = size_t(band_geom<RT>::entries) * sizeof(RT) +
+                                 size_t(LE) * kBandThreads * sizeof(RT);   // band + scratch
+};
+
+template <typename RT, bool WEIGHTED>
+__global__ void __launch_bounds__(kBandThreads, 1) band_reduce2_kernel(const __grid_constant__ band_params P)
+{
+  using G  = band_geom<RT>;
+  using G2 = band_geom2<RT>;
+  constexpr int LE = G2::LE;
+  constexpr int SE = G2::step_edges;
+  static_assert((LE + kMinCell - 1) / kMinCell <= 7, "three ballots count at most 7 cell starts");
+  extern __shared__ __align__(16) unsigned char band_smem[];
+  RT* band = reinterpret_cast<RT*>(band_smem);
+  __shared__ int s_next;
+  __shared__ int s_unit;
+
+  const int tid = threadIdx.x, lane = tid & 31;
+  if (blockIdx.x == 0 && tid == 0) *P.queue_next = 0;
+  if (P.state && P.state->done) return;
+  RT* my = band + G::entries + tid;   // scratch column of this thread: my[i * kBandThreads]
+  const uint32_t lanes_lt = (1u << lane) - 1u;
+  const RT* x   = static_cast<const RT*>(P.x);
+  RT* pval      = static_cast<RT*>(P.pval);
+  const RT* bw  = static_cast<const RT*>(P.bw);
+
+  int cur_band = -1;
+  for (;;) {
+    __syncthreads();  // every warp is done with the previous unit
+    if (tid == 0) s_unit = atomicAdd(P.queue, 1);
+    __syncthreads();
+    const int u = s_unit;
+    if (u >= P.num_groups) break;
+    const band_group grp = P.groups[u];
+    if (grp.band != cur_band) {
+      cur_band            = grp.band;
+      const int64_t first = static_cast<int64_t>(grp.band) << G::bits;
+      const int64_t left  = P.num_minors - first;
+      const int n         = static_cast<int>(left < G::entries ? left : G::entries);
+      const RT* src       = x + first;
+      if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+        constexpr int per = 16 / sizeof(RT);
+        const int nv      = n / per;
+        const int4* s4    = reinterpret_cast<const int4*>(src);
+        int4* d4          = reinterpret_cast<int4*>(band);
+        for (int i = tid; i < nv; i += kBandThreads) d4[i] = __ldg(s4 + i);
+        for (int i = nv * per + tid; i < n; i += kBandThreads) band[i] = src[i];
+      } else {
+        for (int i = tid; i < n; i += kBandThreads) band[i] = src[i];
+      }
+    }
+    if (tid == 0) s_next = grp.task_first;
+    __syncthreads();
+    for (;;) {
+      int ti = 0;
+      if (lane == 0) ti = atomicAdd(&s_next, 1);
+      ti = __shfl_sync(0xffffffffu, ti, 0);
+      if (ti >= grp.task_end) break;
+      const band_task t  = P.tasks[ti];
+      const int64_t a0   = t.first & ~int64_t(7);          // 16-byte aligned start
+      const int lead     = static_cast<int>(t.first - a0);
+      const int total    = lead + t.count;
+      const int steps    = (total + SE - 1) / SE;
+      const uint16_t* ip = P.bidx + a0 + lane * LE;
+      const int32_t* pp  = P.ppos + t.rank_first;   // slots of this task's cells
+      int rank           = 0;              // cell starts met so far (relative to rank_first)
+      RT carry           = RT(0);          // sum of the cell that is open at the step boundary
+      uint4 cur[LE / 8], nxt[LE / 8];
+#pragma unroll
+      for (int q = 0; q < LE / 8; ++q) cur[q] = __ldcs(reinterpret_cast<const uint4*>(ip) + q);
+      for (int st = 0; st < steps; ++st) {
+#pragma unroll
+        for (int q = 0; q < LE / 8; ++q) nxt[q] = make_uint4(0, 0, 0, 0);
+        if (st + 1 < steps) {
+#pragma unroll
+          for (int q = 0; q < LE / 8; ++q)
+            nxt[q] = __ldcs(reinterpret_cast<const uint4*>(ip + (st + 1) * SE) + q);
+        }
+        const int base = st * SE + lane * LE;   // position of the lane's first edge
+        // gathers from the band (every index is a valid band offset, also outside the task)
+        RT v[LE];
+        uint32_t fmask = 0;
+#pragma unroll
+        for (int q = 0; q < LE / 8; ++q) {
+          const uint4 c = cur[q];
+          v[8 * q + 0] = band[c.x & G::mask]; v[8 * q + 1] = band[(c.x >> 16) & G::mask];
+          v[8 * q + 2] = band[c.y & G::mask]; v[8 * q + 3] = band[(c.y >> 16) & G::mask];
+          v[8 * q + 4] = band[c.z & G::mask]; v[8 * q + 5] = band[(c.z >> 16) & G::mask];
+          v[8 * q + 6] = band[c.w & G::mask]; v[8 * q + 7] = band[(c.w >> 16) & G::mask];
+          fmask |= band_flag_bits(c) << (8 * q);
+        }
+        if (WEIGHTED) {
+          // the weight arrays are padded, so this never reads out of bounds
+          const RT* wp = bw + a0 + base;
+          constexpr int per = 16 / sizeof(RT);
+#pragma unroll
+          for (int q = 0; q < LE / per; ++q) {
+            if constexpr (sizeof(RT) == 4) {
+              const float4 w = __ldcs(reinterpret_cast<const float4*>(wp) + q);
+              v[4 * q] *= w.x; v[4 * q + 1] *= w.y; v[4 * q + 2] *= w.z; v[4 * q + 3] *= w.w;
+            } else {
+              const double2 w = __ldcs(reinterpret_cast<const double2*>(wp) + q);
+              v[2 * q] *= w.x; v[2 * q + 1] *= w.y;
+            }
+          }
+        }
+        if (base < lead || base + LE > total) {
+          // first / last lanes of a task: mask what lies outside
+          uint32_t vmask = 0;
+#pragma unroll
+          for (int i = 0; i < LE; ++i) vmask |= ((base + i >= lead && base + i < total) ? 1u : 0u) << i;
+          fmask &= vmask;
+#pragma unroll
+          for (int i = 0; i < LE; ++i)
+            if (!(vmask & (1u << i))) v[i] = RT(0);
+        }
+        // ranks of the lane's cell starts (<= 7 per lane): three ballots give the exclusive prefix
+        const int cnt     = __popc(fmask);
+        const uint32_t b0 = __ballot_sync(0xffffffffu, cnt & 1);
+        const uint32_t b1 = __ballot_sync(0xffffffffu, cnt & 2);
+        const uint32_t b2 = __ballot_sync(0xffffffffu, cnt & 4);
+        const int excl = __popc(b0 & lanes_lt) + 2 * __popc(b1 & lanes_lt) + 4 * __popc(b2 & lanes_lt);
+        const int step_flags = __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
+        // sequential segmented sum inside the lane; the running sum BEFORE every position goes to
+        // the thread's scratch column (only the entries at cell starts are read back)
+        RT run = RT(0);
+#pragma unroll
+        for (int i = 0; i < LE; ++i) {
+          my[i * kBandThreads] = run;   // unconditional: measured faster than a predicated store
+          if (fmask & (1u << i)) run = RT(0);
+          run += v[i];
+        }
+        // segmented inclusive scan of the open tails across the lanes
+        const uint32_t fl = __ballot_sync(0xffffffffu, cnt > 0);
+        const uint32_t le = fl & (lanes_lt | (1u << lane));
+        const int seg0    = le ? 31 - __clz(le) : 0;   // first lane of this lane's segment
+        RT sv = run;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const RT pv = __shfl_up_sync(0xffffffffu, sv, o);
+          if (lane - o >= seg0) sv += pv;
+        }
+        const RT up_v = __shfl_up_sync(0xffffffffu, sv, 1);
+        RT carry_in   = carry;
+        if (lane > 0) carry_in = (fl & lanes_lt) ? up_v : up_v + carry;
+        const RT last_v = __shfl_sync(0xffffffffu, sv, 31);
+        // the cells that end in this lane: one store per cell start, the first one closes the
+        // cell carried into the lane (the task's very first cell start closes nothing)
+        {
+          int r      = rank + excl - 1;
+          uint32_t m = fmask;
+          RT add     = carry_in;
+          while (m) {
+            const int i = __ffs(m) - 1;
+            m &= m - 1;
+            const RT val = my[i * kBandThreads] + add;
+            add          = RT(0);
+            if (r >= 0) pval[__ldg(pp + r)] = val;
+            ++r;
+          }
+        }
+        carry = fl ? last_v : last_v + carry;
+        rank += step_flags;
+#pragma unroll
+        for (int q = 0; q < LE / 8; ++q) cur[q] = nxt[q];
       }
       // the cell that is still open at the end of the task
       if (lane == 0 && rank > 0) pval[__ldg(pp + rank - 1)] = carry;

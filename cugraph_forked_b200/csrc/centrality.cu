@@ -166,6 +166,7 @@ struct pull_launcher {
   edge_partition* kp{nullptr};   // the partition the tiled kernel walks (ep or the reduced one)
   dbuf<RT> pval;
   const RT* kweights{nullptr};   // weights of kp
+  int band_kernel{2};            // phase-1 formulation: 2 = scratch-column kernel, 1 = first one
   dbuf<int32_t> band_queue;      // two unit counters of phase 1, used alternately
   int64_t band_launches{0};
 
@@ -266,6 +267,8 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
       kp       = bl->reduced.get();
       kweights = weighted ? reinterpret_cast<const RT*>(kp->weights.data()) : nullptr;
       pval.alloc(static_cast<size_t>(bl->num_partials), s, 8);
+      // the scratch-column kernel wins only for unweighted 4-byte values (profiles/r1m/)
+      band_kernel = env_int("B200_BAND_KERNEL", (sizeof(RT) == 4 && !weighted) ? 2 : 1) == 1 ? 1 : 2;
       band_queue.alloc(2, s);
       CUDA_TRY(cudaMemsetAsync(band_queue.data(), 0, 8, s));
       band_launches = 0;
@@ -277,6 +280,12 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
         CUDA_TRY(cudaFuncSetAttribute(band_reduce_kernel<RT, false>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       band_geom<RT>::entries * static_cast<int>(sizeof(RT))));
+        CUDA_TRY(cudaFuncSetAttribute(band_reduce2_kernel<RT, true>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      static_cast<int>(band_geom2<RT>::smem)));
+        CUDA_TRY(cudaFuncSetAttribute(band_reduce2_kernel<RT, false>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      static_cast<int>(band_geom2<RT>::smem)));
         configured = true;
       }
     } else {
@@ -350,11 +359,19 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
     ++band_launches;
     B.num_minors      = ep->num_minors;
     B.state           = state;
-    const size_t smem = static_cast<size_t>(band_geom<RT>::entries) * sizeof(RT);
-    if (weighted)
-      band_reduce_kernel<RT, true><<<main_ctas, kBandThreads, smem, s>>>(B);
-    else
-      band_reduce_kernel<RT, false><<<main_ctas, kBandThreads, smem, s>>>(B);
+    if (band_kernel == 2) {
+      const size_t smem = band_geom2<RT>::smem;
+      if (weighted)
+        band_reduce2_kernel<RT, true><<<main_ctas, kBandThreads, smem, s>>>(B);
+      else
+        band_reduce2_kernel<RT, false><<<main_ctas, kBandThreads, smem, s>>>(B);
+    } else {
+      const size_t smem = static_cast<size_t>(band_geom<RT>::entries) * sizeof(RT);
+      if (weighted)
+        band_reduce_kernel<RT, true><<<main_ctas, kBandThreads, smem, s>>>(B);
+      else
+        band_reduce_kernel<RT, false><<<main_ctas, kBandThreads, smem, s>>>(B);
+    }
     CUDA_TRY(cudaGetLastError());
     ++launches;
   }

@@ -181,10 +181,95 @@ def run_task(L, t, x, pval, dtype, minc=3):
         store(int(ppos[pp + rank - 1]), carry)
 
 
-def spmv_banded(L, x, dtype=np.float64, minc=3):
+def run_task2(L, t, x, pval, dtype, le=16):
+    """band_reduce2_kernel, one task on one warp: 32 lanes x `le` edges per step, running sums
+    through a scratch column, cells closed by a loop over the lane's cell-start bits."""
+    bits = L["bits"]
+    mask = (1 << bits) - 1
+    bidx, bw, ppos = L["bidx"], L["bw"], L["ppos"]
+    band0 = t["band"] << bits
+    a0 = t["first"] & ~7
+    lead = t["first"] - a0
+    total = lead + t["count"]
+    se = 32 * le
+    steps = (total + se - 1) // se
+    pp = t["rank_first"]
+    rank = 0
+    carry = dtype(0)
+
+    def store(slot, val):
+        assert np.isnan(pval[slot]), "partial written twice"
+        pval[slot] = val
+
+    for st in range(steps):
+        fm = [0] * 32
+        scratch = [[dtype(0)] * le for _ in range(32)]
+        tails = [dtype(0)] * 32
+        for lane in range(32):
+            base = st * se + lane * le
+            run = dtype(0)
+            for i in range(le):
+                pos = a0 + base + i
+                hv = int(bidx[pos]) if pos < bidx.size else 0
+                valid = lead <= base + i < total
+                v = dtype(0)
+                flag = False
+                if valid:
+                    v = dtype(x[band0 + (hv & mask)])
+                    if bw is not None:
+                        v = dtype(v * bw[pos])
+                    flag = bool(hv & 0x8000)
+                scratch[lane][i] = run
+                if flag:
+                    fm[lane] |= 1 << i
+                    run = dtype(0)
+                run = dtype(run + v)
+            tails[lane] = run
+        cnt = [bin(m).count("1") for m in fm]
+        assert max(cnt) <= 7
+        step_flags = sum(cnt)
+        fl = sum((cnt[l] > 0) << l for l in range(32))
+        sv = list(tails)
+        seg0 = []
+        for lane in range(32):
+            le_m = fl & ((1 << (lane + 1)) - 1)
+            seg0.append(le_m.bit_length() - 1 if le_m else 0)
+        o = 1
+        while o < 32:
+            pv = [sv[l - o] if l >= o else dtype(0) for l in range(32)]
+            for l in range(32):
+                if l - o >= seg0[l]:
+                    sv[l] = dtype(sv[l] + pv[l])
+            o <<= 1
+        for lane in range(32):
+            lt = (1 << lane) - 1
+            carry_in = carry
+            if lane > 0:
+                carry_in = sv[lane - 1] if (fl & lt) else dtype(sv[lane - 1] + carry)
+            r = rank + sum(cnt[:lane]) - 1
+            m = fm[lane]
+            add = carry_in
+            while m:
+                i = (m & -m).bit_length() - 1
+                m &= m - 1
+                val = dtype(scratch[lane][i] + add)
+                add = dtype(0)
+                if r >= 0:
+                    store(int(ppos[pp + r]), val)
+                r += 1
+        carry = sv[31] if fl else dtype(sv[31] + carry)
+        rank += step_flags
+    if rank > 0:
+        store(int(ppos[pp + rank - 1]), carry)
+
+
+def spmv_banded(L, x, dtype=np.float64, minc=3, kernel=1, le=16):
     pval = np.full(L["n_part"], np.nan, dtype)
     for t in L["tasks"]:
-        run_task(L, t, x, pval, dtype, minc)
+        if kernel == 2:
+            run_task2(L, t, x, pval, dtype, le)
+        else:
+            run_task(L, t, x, pval, dtype, minc)
     assert not np.isnan(pval).any(), "a partial was never written"
     xcat = np.concatenate([x.astype(dtype), pval])
     prod = xcat[L["ridx"]]

@@ -50,6 +50,10 @@ def test_two_phase_equals_plain_spmv(bits, cellmax, window, minc, hot_min, weigh
     nz = off[:-1] < off[1:]
     ref[nz] = np.add.reduceat(prod, off[:-1][nz])
     assert np.allclose(y, ref, rtol=1e-12, atol=0)
+    if minc >= 3:
+        for le in (8, 16):
+            y2 = bm.spmv_banded(L, x, minc=minc, kernel=2, le=le)
+            assert np.allclose(y2, ref, rtol=1e-12, atol=0)
     # every task starts at a cell start and tasks tile the banded edges
     pos = 0
     for t in L["tasks"]:
