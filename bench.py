@@ -148,7 +148,7 @@ def run_reference(args, rank, world):
     line = {
         "impl": "reference", "metric": "pagerank_gteps", "value": best["value"], "unit": "GTEPS",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": None, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": None, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": args.dtype, "data": "synthetic",
         "config": {"workload": f"PageRank {args.dtype} on RMAT scale {args.scale} ef {EDGE_FACTOR} "
                                f"({nv} V, {ne} E), a/b/c={A}/{B}/{C}, alpha={ALPHA}",

@@ -22,6 +22,8 @@ if [ -d "$ref/cpp/tests" ]; then
   sed -n '42,130p' "$ref/cpp/tests/link_analysis/pagerank_test.cpp"            > "$tmp/ref_pagerank.inc"
   sed -n '41,93p'  "$ref/cpp/tests/centrality/katz_centrality_test.cpp"        > "$tmp/ref_katz.inc"
   sed -n '41,96p'  "$ref/cpp/tests/centrality/eigenvector_centrality_test.cpp" > "$tmp/ref_eigenvector.inc"
+  sed -n '46,127p' "$ref/cpp/tests/link_analysis/hits_test.cpp"                > "$tmp/ref_hits.inc"
+  grep -q 'hits_reference('                       "$tmp/ref_hits.inc"
   grep -q 'void pagerank_reference'               "$tmp/ref_pagerank.inc"
   grep -q 'void katz_centrality_reference'        "$tmp/ref_katz.inc"
   grep -q 'void eigenvector_centrality_reference' "$tmp/ref_eigenvector.inc"

@@ -19,9 +19,11 @@
 // (cpp/tests/c_api/pagerank_test.c:211-318, katz_test.c:103-129,
 // eigenvector_centrality_test.c:93-108) and against oracle/_ref (the reference's own
 // functions compiled from /root/reference by oracle/build_ref.sh).
+#include <algorithm>
 #include <cmath>
 #include <cstddef>
 #include <cstdint>
+#include <limits>
 #include <vector>
 
 namespace {
@@ -159,9 +161,95 @@ long eigenvector_cpu(const int32_t* src, const int32_t* dst, const R* weights, i
   return done;
 }
 
+// ------------------------------------------------------------------------------------------
+// HITS (the next row of the path).  Restates the reference's host
+// hits_reference (cpp/tests/link_analysis/hits_test.cpp:46-127) with the two switches of the
+// device implementation it checks (cpp/src/link_analysis/hits_impl.cuh:54-185): the final sum
+// normalisation is optional (`normalize`, hits_impl.cuh:166-169; the host function always
+// applies it) and the iteration count can be pinned (`fixed_iterations`).  offsets / indices
+// are the CSR of the graph (rows = sources); weights play no role in HITS.
+// Returns the 0-based index of the iteration that met the tolerance, or max_iterations.
+// ------------------------------------------------------------------------------------------
+// The reference sums with std::reduce / std::transform_reduce, which libstdc++ evaluates for
+// random-access ranges four elements at a time: init += (a0 + a1) + (a2 + a3).  Restated here so
+// that the port stays bit-identical to the compiled reference (tests/test_oracle.py).
+template <typename R, typename F>
+R reduce4(int64_t n, F get)
+{
+  R init = R(0);
+  int64_t i = 0;
+  while (n - i >= 4) {
+    const R v1 = get(i) + get(i + 1);
+    const R v2 = get(i + 2) + get(i + 3);
+    const R v3 = v1 + v2;
+    init       = init + v3;
+    i += 4;
+  }
+  for (; i < n; ++i) init = init + get(i);
+  return init;
+}
+
+template <typename R>
+long hits_cpu(const int64_t* offsets, const int32_t* indices, int64_t nv, long max_iterations,
+              const R* starting_hubs, int normalize, double tolerance, R* hubs_out, R* auth_out,
+              double* error_out, long fixed_iterations)
+{
+  if (nv < 2) return -2;
+  std::vector<R> prev_hubs(nv, R(1) / static_cast<R>(nv)), curr_hubs(nv), curr_auth(nv);
+  if (starting_hubs) {
+    std::copy(starting_hubs, starting_hubs + nv, prev_hubs.begin());
+    const R norm = reduce4<R>(nv, [&](int64_t v) { return prev_hubs[v]; });
+    for (int64_t v = 0; v < nv; ++v) prev_hubs[v] = prev_hubs[v] / norm;
+  }
+  double err = std::numeric_limits<double>::max();
+  const long cap = fixed_iterations > 0 ? fixed_iterations : max_iterations;
+  long it = 0;
+  for (; it < cap; ++it) {
+    std::fill(curr_hubs.begin(), curr_hubs.end(), R(0));
+    std::fill(curr_auth.begin(), curr_auth.end(), R(0));
+    for (int64_t s = 0; s < nv; ++s)
+      for (int64_t e = offsets[s]; e < offsets[s + 1]; ++e) curr_auth[indices[e]] += prev_hubs[s];
+    for (int64_t s = 0; s < nv; ++s)
+      for (int64_t e = offsets[s]; e < offsets[s + 1]; ++e) curr_hubs[s] += curr_auth[indices[e]];
+    R hmax = R(0), amax = R(0);
+    for (int64_t v = 0; v < nv; ++v) hmax = std::max(hmax, curr_hubs[v]);
+    for (int64_t v = 0; v < nv; ++v) curr_hubs[v] = curr_hubs[v] / hmax;
+    for (int64_t v = 0; v < nv; ++v) amax = std::max(amax, curr_auth[v]);
+    for (int64_t v = 0; v < nv; ++v) curr_auth[v] = curr_auth[v] / amax;
+    const R diff =
+      reduce4<R>(nv, [&](int64_t v) { return std::abs(curr_hubs[v] - prev_hubs[v]); });
+    err = static_cast<double>(diff);
+    if (fixed_iterations <= 0 && err < tolerance) break;
+    std::copy(curr_hubs.begin(), curr_hubs.end(), prev_hubs.begin());
+  }
+  if (normalize) {
+    const R hs = reduce4<R>(nv, [&](int64_t v) { return curr_hubs[v]; });
+    for (int64_t v = 0; v < nv; ++v) curr_hubs[v] = curr_hubs[v] / hs;
+    const R as = reduce4<R>(nv, [&](int64_t v) { return curr_auth[v]; });
+    for (int64_t v = 0; v < nv; ++v) curr_auth[v] = curr_auth[v] / as;
+  }
+  std::copy(curr_hubs.begin(), curr_hubs.end(), hubs_out);
+  std::copy(curr_auth.begin(), curr_auth.end(), auth_out);
+  if (error_out) *error_out = err;
+  return it;
+}
+
 }  // namespace
 
 extern "C" {
+
+#define ORACLE_DEFINE_HITS(SUFFIX, R)                                                              \
+  long oracle_hits_##SUFFIX(const int64_t* offsets, const int32_t* indices, int64_t nv,            \
+                            long max_iterations, const R* starting_hubs, int normalize,            \
+                            double tolerance, R* hubs, R* authorities, double* error,              \
+                            long fixed_iterations)                                                 \
+  {                                                                                                \
+    return hits_cpu<R>(offsets, indices, nv, max_iterations, starting_hubs, normalize, tolerance,  \
+                       hubs, authorities, error, fixed_iterations);                                \
+  }
+ORACLE_DEFINE_HITS(f32, float)
+ORACLE_DEFINE_HITS(f64, double)
+
 
 #define ORACLE_DEFINE(SUFFIX, R)                                                                   \
   long oracle_pagerank_##SUFFIX(const int64_t* offsets, const int32_t* indices, const R* weights,  \

@@ -138,6 +138,43 @@ def eigenvector(src, dst, weights=None, *, num_vertices, dtype=np.float32, epsil
     return out, int(rc)
 
 
+def hits(offsets, indices, *, dtype=np.float32, max_iterations=500, tolerance=1e-5,
+         starting_hubs=None, normalize=True, fixed_iterations=0, impl="port"):
+    """HITS on the CSR (rows = sources) of a graph.  Returns (hubs, authorities, error, iterations).
+    impl="ref" runs the reference's own hits_reference (always sum-normalised)."""
+    offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+    indices = np.ascontiguousarray(indices, dtype=np.int32)
+    nv = len(offsets) - 1
+    hubs = np.zeros(nv, dtype=dtype)
+    auth = np.zeros(nv, dtype=dtype)
+    err = ctypes.c_double(0.0)
+    sh = None if starting_hubs is None else np.ascontiguousarray(starting_hubs, dtype=dtype)
+    if impl == "ref":
+        assert normalize and not fixed_iterations
+        fn = getattr(ref_lib(), "ref_hits_" + _sfx(dtype))
+        fn.restype = ctypes.c_long
+        rc = fn(_p(offsets), _p(indices), ctypes.c_int64(nv), ctypes.c_int64(len(indices)),
+                ctypes.c_long(max_iterations), _p(sh), ctypes.c_double(tolerance), _p(hubs),
+                _p(auth), ctypes.byref(err))
+    else:
+        fn = getattr(port_lib(), "oracle_hits_" + _sfx(dtype))
+        fn.restype = ctypes.c_long
+        rc = fn(_p(offsets), _p(indices), ctypes.c_int64(nv), ctypes.c_long(max_iterations), _p(sh),
+                ctypes.c_int(normalize), ctypes.c_double(tolerance), _p(hubs), _p(auth),
+                ctypes.byref(err), ctypes.c_long(fixed_iterations))
+    if rc < 0:
+        raise RuntimeError("HITS: invalid input")
+    return hubs, auth, float(err.value), int(rc)
+
+
+def csr_from_coo(src, dst, num_vertices):
+    """Un-renumbered CSR (rows = sources) in input order, the layout hits_reference walks."""
+    order = np.argsort(src, kind="stable")
+    offsets = np.zeros(num_vertices + 1, dtype=np.int64)
+    np.cumsum(np.bincount(src, minlength=num_vertices), out=offsets[1:])
+    return offsets, np.asarray(dst)[order].astype(np.int32)
+
+
 def csc_from_coo(src, dst, weights, num_vertices):
     """Un-renumbered CSC (rows = destinations) in input order, as the reference tests build the
     host graph for pagerank_reference (pagerank_test.cpp:264-300)."""

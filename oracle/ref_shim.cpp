@@ -7,6 +7,7 @@
 //   ref_pagerank.inc     <- cpp/tests/link_analysis/pagerank_test.cpp:42-130
 //   ref_katz.inc         <- cpp/tests/centrality/katz_centrality_test.cpp:41-93
 //   ref_eigenvector.inc  <- cpp/tests/centrality/eigenvector_centrality_test.cpp:41-96
+//   ref_hits.inc         <- cpp/tests/link_analysis/hits_test.cpp:46-127
 // The only adaptation is the gtest macro: ASSERT_TRUE(x) throws, and the shim turns
 // the exception into a -1 return (the reference aborts the test instead).
 #include <algorithm>
@@ -16,6 +17,7 @@
 #include <numeric>
 #include <optional>
 #include <stdexcept>
+#include <tuple>
 #include <vector>
 
 #define ASSERT_TRUE(cond)                                           \
@@ -23,9 +25,15 @@
     if (!(cond)) throw std::runtime_error("ASSERT_TRUE(" #cond ")"); \
   } while (0)
 
+#define CUGRAPH_EXPECTS(cond, msg)                 \
+  do {                                             \
+    if (!(cond)) throw std::runtime_error(msg);    \
+  } while (0)
+
 #include "ref_pagerank.inc"
 #include "ref_katz.inc"
 #include "ref_eigenvector.inc"
+#include "ref_hits.inc"
 
 extern "C" {
 
@@ -86,5 +94,27 @@ REF_DEFINE(f64, double, int64_t)
 
 REF_DEFINE_EIG(f32, float)
 REF_DEFINE_EIG(f64, double)
+
+// hits_reference always applies the final sum normalisation; returns its iteration count
+#define REF_DEFINE_HITS(SUFFIX, R)                                                               \
+  long ref_hits_##SUFFIX(const int64_t* offsets, const int32_t* indices, int64_t nv, int64_t ne,  \
+                         long max_iterations, const R* starting_hubs, double tolerance, R* hubs,  \
+                         R* authorities, double* error)                                           \
+  {                                                                                              \
+    try {                                                                                        \
+      auto r = hits_reference<R, int32_t, int64_t>(                                              \
+        offsets, indices, static_cast<int32_t>(nv), ne, static_cast<size_t>(max_iterations),     \
+        starting_hubs ? std::optional<const R*>{starting_hubs} : std::nullopt, true, tolerance); \
+      std::copy(std::get<0>(r).begin(), std::get<0>(r).end(), hubs);                             \
+      std::copy(std::get<1>(r).begin(), std::get<1>(r).end(), authorities);                      \
+      if (error) *error = std::get<2>(r);                                                        \
+      return static_cast<long>(std::get<3>(r));                                                  \
+    } catch (std::exception const&) {                                                            \
+      return -1;                                                                                 \
+    }                                                                                            \
+  }
+
+REF_DEFINE_HITS(f32, float)
+REF_DEFINE_HITS(f64, double)
 
 }  // extern "C"

@@ -37,3 +37,30 @@ def nearly_equal(a, b, eps=1e-3):
     a = np.asarray(a, np.float64)
     b = np.asarray(b, np.float64)
     return np.all(np.abs(a - b) <= eps * np.maximum(np.abs(a), np.abs(b)))
+
+
+# cpp/tests/c_api/hits_test.c:155-185 (test_hits) and :221-253 (test_hits_with_initial): graph G6,
+# normalize = FALSE (scores are max-normalised), epsilon 1e-4, 20 iterations at most
+G6_HITS = dict(epsilon=0.0001, max_iterations=20,
+               hubs=np.array([0.347296, 0.532089, 1, 0.00003608, 0.00003608, 0]),
+               authorities=np.array([0.652703, 0.879385, 0, 1, 0.347296, 0.00009136]))
+G6_HITS_INITIAL = dict(epsilon=0.0001, max_iterations=20,
+                       initial_vertices=np.array([0, 1, 2, 3, 4], dtype=np.int32),
+                       initial_hubs=np.array([0.347296, 0.532089, 1, 0.00003608, 0.00003608]),
+                       hubs=np.array([0.347296, 0.532089, 1, 0.00000959, 0.00000959, 0]),
+                       authorities=np.array([0.652704, 0.879385, 0, 1, 0.347296, 0.00002428]))
+# cpp/tests/c_api/hits_test.c:255-300 (test_hits_bigger): 54 vertices, 48 edges, epsilon 1e-6,
+# 100 iterations at most, normalize = FALSE
+H54_SRC = np.array([29, 45, 6, 8, 16, 45, 8, 16, 6, 38, 45, 45, 48, 45, 45, 45,
+                    45, 48, 53, 45, 6, 45, 38, 45, 38, 45, 16, 45, 38, 16, 45, 45,
+                    38, 6, 38, 45, 45, 45, 16, 38, 6, 45, 29, 45, 29, 6, 38, 6], dtype=np.int32)
+H54_DST = np.array([45, 45, 16, 45, 6, 45, 45, 16, 45, 38, 45, 6, 45, 38, 16, 45,
+                    45, 45, 45, 53, 29, 16, 45, 8, 8, 16, 45, 38, 45, 6, 45, 45,
+                    6, 6, 16, 38, 16, 45, 45, 6, 16, 6, 53, 16, 38, 45, 45, 16], dtype=np.int32)
+_h54_hubs = np.zeros(54)
+_h54_hubs[[6, 8, 16, 29, 38, 45, 48, 53]] = [0.323569, 0.156401, 0.253312, 0.110617, 0.365733, 1,
+                                             0.156401, 0.0782005]
+_h54_auth = np.zeros(54)
+_h54_auth[[6, 8, 16, 29, 38, 45, 53]] = [0.321874, 0.123424, 0.595522, 0.0292397, 0.314164, 1,
+                                         0.100368]
+H54_HITS = dict(epsilon=0.000001, max_iterations=100, hubs=_h54_hubs, authorities=_h54_auth)

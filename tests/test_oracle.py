@@ -112,3 +112,53 @@ def test_mtx_loader_matches_reference_expansion():
     assert sym and nv == 1589 and len(src) == 5484
     assert np.array_equal(src[0::2], dst[1::2]) and np.array_equal(dst[0::2], src[1::2])
     assert np.array_equal(w[0::2], w[1::2])
+
+
+# ----------------------------------------------------------------------------------------------
+# HITS (the next row): the restatement is pinned to the reference's own
+# hits_reference (bit-identical when sum-normalised) and to the golden vectors of
+# cpp/tests/c_api/hits_test.c (max-normalised, relative 1e-3)
+# ----------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_hits_port_is_bit_identical_to_reference(oracle_built, dtype):
+    from oracle import cpu_oracle as co
+    if not co.ref_available():
+        pytest.skip("oracle/_ref not built")
+    cases = []
+    for name in ("karate.mtx", "dolphins.mtx", "netscience.mtx"):
+        src, dst, _, nv, _ = util.load_mtx(name, dtype)
+        cases.append((src, dst, nv))
+    src, dst = util.rmat(10, seed=4)
+    cases.append((src, dst, 1 << 10))
+    rng = np.random.default_rng(5)
+    for src, dst, nv in cases:
+        off, idx = co.csr_from_coo(src, dst, nv)
+        for start in (None, rng.random(nv).astype(dtype)):
+            a = co.hits(off, idx, dtype=dtype, max_iterations=200, tolerance=1e-6,
+                        starting_hubs=start, impl="ref")
+            b = co.hits(off, idx, dtype=dtype, max_iterations=200, tolerance=1e-6,
+                        starting_hubs=start, impl="port")
+            assert a[3] == b[3] and a[2] == b[2]
+            assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+
+
+def test_hits_golden_vectors(oracle_built):
+    from oracle import cpu_oracle as co
+    off, idx = co.csr_from_coo(gv.G6_SRC, gv.G6_DST, 6)
+    p = gv.G6_HITS
+    hubs, auth, _, it = co.hits(off, idx, dtype=np.float64, max_iterations=p["max_iterations"],
+                                tolerance=p["epsilon"], normalize=False)
+    assert it < p["max_iterations"]
+    assert gv.nearly_equal(hubs, p["hubs"]) and gv.nearly_equal(auth, p["authorities"])
+    p = gv.G6_HITS_INITIAL
+    start = np.zeros(6)
+    start[p["initial_vertices"]] = p["initial_hubs"]
+    hubs, auth, _, _ = co.hits(off, idx, dtype=np.float64, max_iterations=p["max_iterations"],
+                               tolerance=p["epsilon"], starting_hubs=start, normalize=False)
+    assert gv.nearly_equal(hubs, p["hubs"]) and gv.nearly_equal(auth, p["authorities"])
+    off, idx = co.csr_from_coo(gv.H54_SRC, gv.H54_DST, 54)
+    p = gv.H54_HITS
+    for dtype in (np.float32, np.float64):
+        hubs, auth, _, _ = co.hits(off, idx, dtype=dtype, max_iterations=p["max_iterations"],
+                                   tolerance=p["epsilon"], normalize=False)
+        assert gv.nearly_equal(hubs, p["hubs"]) and gv.nearly_equal(auth, p["authorities"])
