@@ -107,6 +107,18 @@ class EigenvectorParams(ctypes.Structure):
     ]
 
 
+class HitsParams(ctypes.Structure):
+    _fields_ = [
+        ("epsilon", ctypes.c_double),
+        ("max_iterations", ctypes.c_uint64),
+        ("value_type", ctypes.c_int32),
+        ("has_initial_hubs_guess", ctypes.c_int32),
+        ("normalize", ctypes.c_int32),
+        ("pad", ctypes.c_int32),
+        ("fixed_iterations", ctypes.c_int64),
+    ]
+
+
 # every symbol include/b200_cugraph.h declares: name -> (restype, argtypes)
 _vp, _sz, _i, _d, _u64 = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_double, ctypes.c_uint64
 _pp = ctypes.POINTER(ctypes.c_void_p)
@@ -133,6 +145,8 @@ SIGNATURES = {
                                   ctypes.POINTER(CentralityStats)]),
     "b200_eigenvector_centrality": (_i, [_vp, _vp, ctypes.POINTER(EigenvectorParams), _vp,
                                          ctypes.POINTER(CentralityStats)]),
+    "b200_hits": (_i, [_vp, _vp, ctypes.POINTER(HitsParams), _vp, _vp,
+                       ctypes.POINTER(CentralityStats)]),
     "b200_generate_rmat_edgelist": (_i, [_vp, _i, _sz, _d, _d, _d, _u64, _i, _u64, _i, _vp, _vp]),
     "b200_uniform_fill": (_i, [_vp, _i, _vp, _sz, _u64]),
     "b200_build_info": (ctypes.c_char_p, []),

@@ -343,6 +343,16 @@ int b200_eigenvector_centrality(b200_handle_t* h, b200_graph_t* g,
   });
 }
 
+int b200_hits(b200_handle_t* h, b200_graph_t* g, const b200_hits_params_t* p, void* hubs,
+              void* authorities, b200_centrality_stats_t* stats)
+{
+  return guarded([&] {
+    B200_EXPECTS(h != nullptr, kInvalidHandle, "invalid handle");
+    B200_EXPECTS(g && p, kInvalidInput, "NULL argument");
+    hits(h, g, p, hubs, authorities, stats);
+  });
+}
+
 int b200_generate_rmat_edgelist(b200_handle_t* h, int scale, size_t num_edges, double a, double b,
                                 double c, uint64_t seed, int clip_and_flip, uint64_t first_edge,
                                 int vertex_type, void* src, void* dst)

@@ -14,6 +14,9 @@ void eigenvector_centrality(b200_handle* h, b200_graph* g, const b200_eigenvecto
                             void* out, b200_centrality_stats_t* stats);
 void spmv_pull(b200_handle* h, b200_graph* g, int value_type, const void* x, double scale,
                double init, void* y);
+// hits.cu
+void hits(b200_handle* h, b200_graph* g, const b200_hits_params_t* p, void* hubs, void* authorities,
+          b200_centrality_stats_t* stats);
 
 // one edge partition's SpMV with the raw epilogue (centrality.cu), used by the multi-GPU drivers
 struct partition_spmv;

@@ -234,6 +234,9 @@ struct b200_graph {
   // sorted (external id, internal id) pairs of the local vertices, built on first use
   b200::dbuf<uint64_t> ext_sorted;
   b200::dbuf<uint32_t> ext_internal;
+  // HITS companions (hits.cu), built on first use: the same graph with rows = sources (CSR) and,
+  // for a weighted graph, a weight-less copy with rows = destinations; internal ids
+  std::shared_ptr<b200_graph> hits_csr, hits_csc;
   bool have_ext_map{false};
   // the COO in external ids is not kept; a graph stored the other way round is rebuilt from a
   // decompressed edge list when a pull algorithm needs it (c_api/graph.hpp:44-79 does the same)

@@ -281,6 +281,24 @@ def eigenvector_centrality(graph: Graph, *, epsilon=1e-6, max_iterations=500, dt
     return c, _stats(st)
 
 
+def hits(graph: Graph, *, epsilon=1e-5, max_iterations=100, dtype=torch.float32,
+         initial_hubs_guess=None, normalize=True, fixed_iterations=0):
+    """cugraph::hits: returns (hubs, authorities, stats) in internal vertex order;
+    stats.iterations is the reference's final_iteration_count, stats.last_diff its hub score
+    difference."""
+    n = graph.num_local_vertices
+    hubs = torch.zeros(n, dtype=dtype, device="cuda") if initial_hubs_guess is None \
+        else _dev(initial_hubs_guess, dtype).clone()
+    auth = torch.zeros(n, dtype=dtype, device="cuda")
+    p = _lib.HitsParams(epsilon, max_iterations, _DT[dtype], int(initial_hubs_guess is not None),
+                        int(normalize), 0, fixed_iterations)
+    st = _lib.CentralityStats()
+    torch.cuda.current_stream().synchronize()
+    check(_lib.lib().b200_hits(graph.handle._h, graph._g, ctypes.byref(p), _ptr(hubs), _ptr(auth),
+                               ctypes.byref(st)))
+    return hubs, auth, _stats(st)
+
+
 def generate_rmat_edgelist(handle: Handle, scale: int, num_edges: int, a=0.57, b=0.19, c=0.19,
                            seed=0, clip_and_flip=False, first_edge=0, dtype=torch.int32):
     """cugraph::generate_rmat_edgelist: returns (src, dst) device tensors."""

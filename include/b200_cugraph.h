@@ -191,6 +191,23 @@ int b200_eigenvector_centrality(b200_handle_t* h, b200_graph_t* g,
                                 const b200_eigenvector_params_t* p, void* centralities,
                                 b200_centrality_stats_t* stats);
 
+typedef struct b200_hits_params {
+  double epsilon;
+  uint64_t max_iterations;
+  int32_t value_type;
+  int32_t has_initial_hubs_guess;  /* hubs[] holds the guess on entry (internal order)            */
+  int32_t normalize;               /* 1: final scores are divided by their sums                    */
+  int32_t pad;
+  int64_t fixed_iterations;        /* > 0: run exactly this many iterations, no stop test          */
+} b200_hits_params_t;
+
+/* cugraph::hits (algorithms.hpp:1224-1234; hits_impl.cuh:54-185).  Single-GPU graphs stored
+ * transposed.  stats->iterations = 0-based index of the iteration that met epsilon, or
+ * max_iterations (the reference's final_iteration_count); stats->last_diff = L1 difference of
+ * the hub scores of the last two iterations. */
+int b200_hits(b200_handle_t* h, b200_graph_t* g, const b200_hits_params_t* p, void* hubs,
+              void* authorities, b200_centrality_stats_t* stats);
+
 /* -------------------------------------------------------------------------------------------
  * R-MAT generator — cugraph::generate_rmat_edgelist
  * (cpp/src/generators/generate_rmat_edgelist.cu:35-111).  Edges [first_edge, first_edge +
