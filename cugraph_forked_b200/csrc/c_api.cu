@@ -57,6 +57,15 @@ struct centrality_result_t {
   device_array_t* values{nullptr};
 };
 
+// c_api/hits.cpp:34-40
+struct hits_result_t {
+  device_array_t* vertex_ids{nullptr};
+  device_array_t* hubs{nullptr};
+  device_array_t* authorities{nullptr};
+  double hub_score_differences{0.0};
+  size_t number_of_iterations{0};
+};
+
 inline size_t type_size(data_type_id_t t) { return (t == INT32 || t == FLOAT32) ? 4 : 8; }
 
 inline cugraph_error_code_t fail(cugraph_error_t** error, int code, const char* msg)
@@ -673,6 +682,101 @@ cugraph_error_code_t cugraph_eigenvector_centrality(const cugraph_resource_handl
     p.value_type     = G->weight_type;
     eigenvector_centrality(h, g, &p, values->buf.data(), nullptr);
     *result = reinterpret_cast<cugraph_centrality_result_t*>(make_result(h, G, values.release()));
+  });
+}
+
+// ---- HITS (c_api/hits.cpp) --------------------------------------------------------------------
+cugraph_type_erased_device_array_view_t* cugraph_hits_result_get_vertices(cugraph_hits_result_t* result)
+{
+  auto* r = reinterpret_cast<hits_result_t*>(result);
+  return cugraph_type_erased_device_array_view(
+    reinterpret_cast<cugraph_type_erased_device_array_t*>(r->vertex_ids));
+}
+cugraph_type_erased_device_array_view_t* cugraph_hits_result_get_hubs(cugraph_hits_result_t* result)
+{
+  auto* r = reinterpret_cast<hits_result_t*>(result);
+  return cugraph_type_erased_device_array_view(
+    reinterpret_cast<cugraph_type_erased_device_array_t*>(r->hubs));
+}
+cugraph_type_erased_device_array_view_t* cugraph_hits_result_get_authorities(
+  cugraph_hits_result_t* result)
+{
+  auto* r = reinterpret_cast<hits_result_t*>(result);
+  return cugraph_type_erased_device_array_view(
+    reinterpret_cast<cugraph_type_erased_device_array_t*>(r->authorities));
+}
+double cugraph_hits_result_get_hub_score_differences(cugraph_hits_result_t* result)
+{
+  return reinterpret_cast<hits_result_t*>(result)->hub_score_differences;
+}
+size_t cugraph_hits_result_get_number_of_iterations(cugraph_hits_result_t* result)
+{
+  return reinterpret_cast<hits_result_t*>(result)->number_of_iterations;
+}
+void cugraph_hits_result_free(cugraph_hits_result_t* result)
+{
+  auto* r = reinterpret_cast<hits_result_t*>(result);
+  if (!r) return;
+  delete r->vertex_ids;
+  delete r->hubs;
+  delete r->authorities;
+  delete r;
+}
+
+cugraph_error_code_t cugraph_hits(
+  const cugraph_resource_handle_t* handle, cugraph_graph_t* graph, double epsilon,
+  size_t max_iterations, const cugraph_type_erased_device_array_view_t* initial_hubs_guess_vertices,
+  const cugraph_type_erased_device_array_view_t* initial_hubs_guess_values, bool_t normalize, bool_t,
+  cugraph_hits_result_t** result, cugraph_error_t** error)
+{
+  *result = nullptr;
+  *error  = nullptr;
+  auto* r = reinterpret_cast<const resource_handle_t*>(handle);
+  auto* G = reinterpret_cast<graph_t*>(graph);
+  CAPI_EXPECTS(r && r->h, CUGRAPH_INVALID_HANDLE, "invalid resource handle", error);
+  CAPI_EXPECTS(G && G->g, CUGRAPH_INVALID_INPUT, "graph is NULL", error);
+  auto view = [](const cugraph_type_erased_device_array_view_t* v) {
+    return reinterpret_cast<const device_array_view_t*>(v);
+  };
+  // hits.cpp:228-239
+  CAPI_EXPECTS((initial_hubs_guess_vertices == nullptr) == (initial_hubs_guess_values == nullptr),
+               CUGRAPH_INVALID_INPUT,
+               "initial_hubs_guess_vertices and initial_hubs_guess_values must be given together",
+               error);
+  CAPI_EXPECTS(!initial_hubs_guess_vertices ||
+                 view(initial_hubs_guess_vertices)->type == G->vertex_type,
+               CUGRAPH_INVALID_INPUT,
+               "vertex type of graph and initial_hubs_guess_vertices must match", error);
+  CAPI_EXPECTS(!initial_hubs_guess_values || view(initial_hubs_guess_values)->type == G->weight_type,
+               CUGRAPH_INVALID_INPUT,
+               "weight type of graph and initial_hubs_guess_values must match", error);
+  return run(error, [&] {
+    b200_handle* h = r->h;
+    b200_graph* g  = G->g;
+    // HITS expects store_transposed == true (hits.cpp:94-100)
+    if (!g->store_transposed) graph_transpose_storage(h, g);
+    size_t nloc = static_cast<size_t>(g->local_last - g->local_first);
+    std::unique_ptr<device_array_t> hubs(make_array(h, nloc, G->weight_type));
+    std::unique_ptr<device_array_t> auth(make_array(h, nloc, G->weight_type));
+    b200_hits_params_t p{};
+    p.epsilon        = epsilon;
+    p.max_iterations = max_iterations;
+    p.value_type     = G->weight_type;
+    p.normalize      = normalize ? 1 : 0;
+    dbuf<char> guess_dense;
+    if (initial_hubs_guess_values) {
+      collect_dense(h, g, view(initial_hubs_guess_vertices), view(initial_hubs_guess_values),
+                    G->weight_type, guess_dense);
+      CUDA_TRY(cudaMemcpyAsync(hubs->buf.data(), guess_dense.data(), nloc * type_size(G->weight_type),
+                               cudaMemcpyDeviceToDevice, h->stream));
+      p.has_initial_hubs_guess = 1;
+    }
+    b200_centrality_stats_t st{};
+    hits(h, g, &p, hubs->buf.data(), auth->buf.data(), &st);
+    std::unique_ptr<centrality_result_t> ids(make_result(h, G, nullptr));
+    auto* out = new hits_result_t{ids->vertex_ids, hubs.release(), auth.release(), st.last_diff,
+                                  static_cast<size_t>(st.iterations)};
+    *result = reinterpret_cast<cugraph_hits_result_t*>(out);
   });
 }
 

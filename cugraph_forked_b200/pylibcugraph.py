@@ -65,6 +65,13 @@ _C_SIGNATURES = {
     "cugraph_katz_centrality": (c_int, [_P, _P, _P, c_double, c_double, c_double, c_size_t, c_int,
                                         _PP, _PP]),
     "cugraph_eigenvector_centrality": (c_int, [_P, _P, c_double, c_size_t, c_int, _PP, _PP]),
+    "cugraph_hits": (c_int, [_P, _P, c_double, c_size_t, _P, _P, c_int, c_int, _PP, _PP]),
+    "cugraph_hits_result_get_vertices": (_P, [_P]),
+    "cugraph_hits_result_get_hubs": (_P, [_P]),
+    "cugraph_hits_result_get_authorities": (_P, [_P]),
+    "cugraph_hits_result_get_hub_score_differences": (c_double, [_P]),
+    "cugraph_hits_result_get_number_of_iterations": (c_size_t, [_P]),
+    "cugraph_hits_result_free": (None, [_P]),
     "cugraph_centrality_result_get_vertices": (_P, [_P]),
     "cugraph_centrality_result_get_values": (_P, [_P]),
     "cugraph_centrality_result_free": (None, [_P]),
@@ -352,3 +359,23 @@ def eigenvector_centrality(resource_handle, graph, epsilon, max_iterations, do_e
         int(do_expensive_check), byref(res), byref(err))
     assert_success(code, err, "cugraph_eigenvector_centrality")
     return _finish(res)
+
+
+def hits(resource_handle, graph, tol, max_iter, initial_hubs_guess_vertices,
+         initial_hubs_guess_values, normalized, do_expensive_check):
+    """hits.pyx:58.  Returns (vertices, hubs, authorities)."""
+    _assert_cai(initial_hubs_guess_vertices, "initial_hubs_guess_vertices", allow_none=True)
+    _assert_cai(initial_hubs_guess_values, "initial_hubs_guess_values", allow_none=True)
+    v = [_View(a) for a in (initial_hubs_guess_vertices, initial_hubs_guess_values)]
+    res, err = c_void_p(), c_void_p()
+    _sync_inputs()
+    c = _c()
+    code = c.cugraph_hits(resource_handle.c_resource_handle_ptr, graph.c_graph_ptr, tol, max_iter,
+                          v[0].ptr, v[1].ptr, int(normalized), int(do_expensive_check), byref(res),
+                          byref(err))
+    assert_success(code, err, "cugraph_hits")
+    vertices = _copy_out(c.cugraph_hits_result_get_vertices(res))
+    hubs = _copy_out(c.cugraph_hits_result_get_hubs(res))
+    authorities = _copy_out(c.cugraph_hits_result_get_authorities(res))
+    c.cugraph_hits_result_free(res)
+    return vertices, hubs, authorities

@@ -96,3 +96,35 @@ def test_hits_errors(handle):
     g2 = engine.Graph(handle, torch.from_numpy(src), torch.from_numpy(dst), store_transposed=False)
     with pytest.raises(engine.CugraphError, match="stored transposed"):
         engine.hits(g2)
+
+
+@pytest.mark.parametrize("store_transposed", [True, False])
+@pytest.mark.parametrize("renumber", [True, False])
+def test_hits_c_api_golden(store_transposed, renumber):
+    """cugraph_hits through the pylibcugraph mirror: hits_test.c test_hits (:155),
+    test_hits_with_transpose (:187, store_transposed = FALSE forces the in-place transpose),
+    test_hits_with_initial (:221) and test_hits_bigger (:255)."""
+    from cugraph_forked_b200 import pylibcugraph as plc
+    from tests.test_gpu_c_api import _by_vertex, _sg, _t
+    rh = plc.ResourceHandle()
+    g = _sg(plc, rh, gv.G6_SRC, gv.G6_DST, gv.G6_WGT, store_transposed, renumber)
+    p = gv.G6_HITS
+    vertices, hubs, auth = plc.hits(rh, g, p["epsilon"], p["max_iterations"], None, None, False, False)
+    assert gv.nearly_equal(_by_vertex(vertices, hubs, 6), p["hubs"])
+    assert gv.nearly_equal(_by_vertex(vertices, auth, 6), p["authorities"])
+    p = gv.G6_HITS_INITIAL
+    vertices, hubs, auth = plc.hits(rh, g, p["epsilon"], p["max_iterations"],
+                                    _t(p["initial_vertices"]),
+                                    _t(p["initial_hubs"].astype(np.float32)), False, False)
+    assert gv.nearly_equal(_by_vertex(vertices, hubs, 6), p["hubs"])
+    assert gv.nearly_equal(_by_vertex(vertices, auth, 6), p["authorities"])
+    # normalize = TRUE: scores sum to 1 and keep their proportions
+    vertices, hubs_n, auth_n = plc.hits(rh, g, gv.G6_HITS["epsilon"], 20, None, None, True, False)
+    h = _by_vertex(vertices, hubs_n, 6)
+    assert abs(h.sum() - 1.0) < 1e-6 and gv.nearly_equal(h / h.max(), gv.G6_HITS["hubs"])
+    # the vertex list of a non-renumbered graph spans 0..max id, so H54 needs renumbering off too
+    g = _sg(plc, rh, gv.H54_SRC, gv.H54_DST, np.ones(48), store_transposed, False)
+    p = gv.H54_HITS
+    vertices, hubs, auth = plc.hits(rh, g, p["epsilon"], p["max_iterations"], None, None, False, False)
+    assert gv.nearly_equal(_by_vertex(vertices, hubs, 54), p["hubs"])
+    assert gv.nearly_equal(_by_vertex(vertices, auth, 54), p["authorities"])
