@@ -22,6 +22,7 @@
 #include <cstddef>
 #include <cstdint>
 #include <optional>
+#include <tuple>
 #include <stdexcept>
 #include <string>
 #include <type_traits>
@@ -190,6 +191,31 @@ void eigenvector_centrality(b200::handle_t const& handle,
   p.has_initial_guess = has_initial_centralities ? 1 : 0;
   b200::check(b200_eigenvector_centrality(handle.get(), graph_view.get(), &p, centralities, nullptr),
               "eigenvector_centrality");
+}
+
+// cugraph::hits (cpp/include/cugraph/algorithms.hpp:1224-1234): returns (sum of the differences of
+// the hub scores of the last two iterations, iteration count).  Single-GPU graphs.
+template <typename vertex_t, typename edge_t, typename weight_t, bool multi_gpu>
+std::tuple<weight_t, size_t> hits(b200::handle_t const& handle,
+                                  graph_view_t<vertex_t, edge_t, weight_t, true, multi_gpu> const& graph_view,
+                                  weight_t* hubs,
+                                  weight_t* authorities,
+                                  weight_t epsilon,
+                                  size_t max_iterations,
+                                  bool has_initial_hubs_guess,
+                                  bool normalize,
+                                  bool do_expensive_check)
+{
+  (void)do_expensive_check;
+  b200_hits_params_t p{};
+  p.epsilon                = static_cast<double>(epsilon);
+  p.max_iterations         = max_iterations;
+  p.value_type             = b200::dtype_id<weight_t>();
+  p.has_initial_hubs_guess = has_initial_hubs_guess ? 1 : 0;
+  p.normalize              = normalize ? 1 : 0;
+  b200_centrality_stats_t st{};
+  b200::check(b200_hits(handle.get(), graph_view.get(), &p, hubs, authorities, &st), "hits");
+  return std::make_tuple(static_cast<weight_t>(st.last_diff), static_cast<size_t>(st.iterations));
 }
 
 }  // namespace cugraph
