@@ -1,4 +1,4 @@
-// TEST INFRASTRUCTURE ONLY — CPU oracle for the PageRank / Katz / eigenvector hot path.
+// TEST INFRASTRUCTURE ONLY — CPU oracle for the PageRank / Katz / eigenvector / HITS hot path.
 //
 // Plain C++17 restatement of the reference's host-side oracles. Only tests/,
 // __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
@@ -9,6 +9,7 @@
 //   pagerank_reference          /root/reference/cpp/tests/link_analysis/pagerank_test.cpp:42-130
 //   katz_centrality_reference   /root/reference/cpp/tests/centrality/katz_centrality_test.cpp:41-93
 //   eigenvector_..._reference   /root/reference/cpp/tests/centrality/eigenvector_centrality_test.cpp:41-96
+//   hits_reference              /root/reference/cpp/tests/link_analysis/hits_test.cpp:46-127
 //
 // Differences from the reference (none change a converged result):
 //   * non-convergence returns -1 instead of tripping a gtest ASSERT;
@@ -17,7 +18,7 @@
 //   * the executed iteration count is returned.
 // Pinned by tests/test_oracle.py against the C-API golden vectors
 // (cpp/tests/c_api/pagerank_test.c:211-318, katz_test.c:103-129,
-// eigenvector_centrality_test.c:93-108) and against oracle/_ref (the reference's own
+// eigenvector_centrality_test.c:93-108, hits_test.c) and against oracle/_ref (the reference's own
 // functions compiled from /root/reference by oracle/build_ref.sh).
 #include <algorithm>
 #include <cmath>
