@@ -1,0 +1,157 @@
+"""GPU: the cugraph-shaped Python callers (cugraph_forked_b200/cugraph.py) on the CUDA library,
+against the golden vectors of the reference's Python tests
+(python/cugraph/cugraph/tests/test_katz_centrality.py:152-173,
+test_eigenvector_centrality.py:136-153), the C-API golden vectors and the oracle.  The table
+logic itself is covered on the CPU by tests/test_python_callers.py; this file checks that the same
+calls land on the library.  (Named to sort after the kernel parity tests.)"""
+import numpy as np
+import pandas as pd
+import pytest
+import torch
+
+from tests import golden_vectors as gv
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def cugraph():
+    from cugraph_forked_b200 import cugraph as cg
+    assert cg._DEVICE == "cuda" and cg._plc.__name__ == "cugraph_forked_b200.pylibcugraph"
+    return cg
+
+
+def _karate():
+    src, dst, w, nv, _ = util.load_mtx("karate.mtx")
+    return src.astype(np.int32), dst.astype(np.int32), w.astype(np.float32)
+
+
+def _scores(df, column, nv):
+    v = df["vertex"].cpu().numpy()
+    assert df[column].is_cuda and sorted(v.tolist()) == list(range(nv))
+    out = np.empty(nv, np.float64)
+    out[v] = df[column].cpu().numpy()
+    return out
+
+
+def _toy(cugraph, src=gv.G6_SRC, dst=gv.G6_DST, w=gv.G6_WGT):
+    G = cugraph.Graph(directed=True)
+    G.from_cudf_edgelist({"s": src, "d": dst, "w": w}, "s", "d", "w", store_transposed=True)
+    return G
+
+
+def test_toy_golden_vectors(cugraph):
+    G = _toy(cugraph)
+    p = gv.G6_PAGERANK
+    df = cugraph.pagerank(G, alpha=p["alpha"], tol=p["epsilon"], max_iter=p["max_iterations"])
+    assert gv.nearly_equal(_scores(df, "pagerank", 6), p["result"])
+    ck = cugraph.katz_centrality(G, alpha=0.01, beta=1.0, tol=0.000001, max_iter=1000)
+    want = [0.410614, 0.403211, 0.390689, 0.415175, 0.395125, 0.433226]
+    assert np.abs(_scores(ck, "katz_centrality", 6) - want).max() <= 1e-2
+    assert gv.nearly_equal(_scores(ck, "katz_centrality", 6), gv.G6_KATZ["result"])
+    h = gv.G6_HITS
+    df = cugraph.hits(G, max_iter=h["max_iterations"], tol=h["epsilon"], normalized=False)
+    assert gv.nearly_equal(_scores(df, "hubs", 6), h["hubs"])
+    assert gv.nearly_equal(_scores(df, "authorities", 6), h["authorities"])
+    q = gv.G6_HITS_INITIAL
+    df = cugraph.hits(G, max_iter=q["max_iterations"], tol=q["epsilon"], normalized=False,
+                      nstart={"vertex": q["initial_vertices"], "values": q["initial_hubs"]})
+    assert gv.nearly_equal(_scores(df, "hubs", 6), q["hubs"])
+    E = _toy(cugraph, gv.E6_SRC, gv.E6_DST, gv.E6_WGT)
+    ck = cugraph.eigenvector_centrality(E, tol=1e-6, max_iter=200)
+    want = [0.236325, 0.292055, 0.458457, 0.60533, 0.190498, 0.495942]
+    assert np.abs(_scores(ck, "eigenvector_centrality", 6) - want).max() <= 1e-4
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_pagerank_karate_all_inputs(cugraph, oracle_built, dtype):
+    src, dst, w = _karate()
+    w = w.astype(dtype)
+    nv = 34
+    G = cugraph.Graph(directed=True)
+    G.from_cudf_edgelist({"0": src, "1": dst, "2": w}, "0", "1", "2", store_transposed=True)
+    pv = np.array([3, 17, 26, 30], np.int32)
+    pw = np.array([0.4, 0.3, 0.2, 0.1], dtype)
+    eps = 1e-6 if dtype == np.float32 else 1e-10
+    want, _ = util.oracle_pagerank(src, dst, w, nv, dtype=np.float64, alpha=0.85, epsilon=1e-12,
+                                   max_iterations=1000, personalization=(pv, pw))
+    ow = np.zeros(nv, dtype)
+    np.add.at(ow, src, w)
+    perm = np.random.default_rng(0).permutation(nv).astype(np.int32)
+    df = cugraph.pagerank(
+        G, alpha=0.85, tol=eps, max_iter=1000,
+        personalization={"vertex": pv, "values": pw},
+        nstart=pd.DataFrame({"vertex": perm, "values": np.full(nv, 1 / nv, dtype)}),
+        precomputed_vertex_out_weight={"vertex": np.arange(nv, dtype=np.int32), "sums": ow})
+    assert df["pagerank"].dtype == (torch.float32 if dtype == np.float32 else torch.float64)
+    assert np.abs(_scores(df, "pagerank", nv) - want).max() <= (1e-5 if dtype == np.float32 else 1e-9)
+
+
+def test_pagerank_string_and_multi_column_labels(cugraph, oracle_built):
+    src, dst, w = _karate()
+    want, _ = util.oracle_pagerank(src, dst, w, 34, dtype=np.float64, alpha=0.85, epsilon=1e-12,
+                                   max_iterations=1000)
+    names = np.array([f"v{i:02d}" for i in range(34)])
+    G = cugraph.Graph(directed=True)
+    G.from_cudf_edgelist(pd.DataFrame({"a": names[src], "b": names[dst], "w": w}), "a", "b", "w",
+                         store_transposed=True)
+    df = cugraph.pagerank(G, tol=1e-6, max_iter=500).sort_values("vertex")
+    assert df["vertex"].tolist() == names.tolist()
+    assert np.abs(df["pagerank"].cpu().numpy() - want).max() <= 1e-5
+    M = pd.DataFrame({"src_0": src, "dst_0": dst, "src_1": src + 1000, "dst_1": dst + 1000,
+                      "weights": w})
+    G = cugraph.Graph(directed=True)
+    G.from_cudf_edgelist(M, source=["src_0", "src_1"], destination=["dst_0", "dst_1"],
+                         edge_attr="weights", store_transposed=True)
+    df = cugraph.pagerank(G, tol=1e-6, max_iter=500)
+    assert df.columns == ["0_vertex", "1_vertex", "pagerank"]
+    df = df.sort_values("0_vertex")
+    assert df["1_vertex"].tolist() == [i + 1000 for i in range(34)]
+    assert np.abs(df["pagerank"].cpu().numpy() - want).max() <= 1e-5
+
+
+def test_undirected_unweighted_graph(cugraph, oracle_built):
+    """Graph() symmetrizes; an unweighted edge list computes in float32 with unit weights;
+    katz_centrality's default alpha is 1 / (largest degree)."""
+    src, dst, _ = _karate()
+    keep = src < dst
+    G = cugraph.Graph()
+    G.from_cudf_edgelist({"0": torch.from_numpy(src[keep]).cuda(),
+                          "1": torch.from_numpy(dst[keep]).cuda()}, "0", "1",
+                         store_transposed=True)
+    assert G.number_of_edges() == int(keep.sum()) and G.number_of_vertices() == 34
+    el = G.edgelist.edgelist_df
+    s, d = el["src"].cpu().numpy(), el["dst"].cpu().numpy()
+    assert len(s) == 2 * int(keep.sum())
+    deg = G.degree()
+    assert deg["degree"].tolist() == (np.bincount(s, minlength=34) * 2).tolist()
+    alpha = 1 / int(deg["degree"].max())
+    want, _ = util.oracle_katz(s, d, None, 34, dtype=np.float64, alpha=alpha, beta=1.0,
+                               epsilon=1e-12, max_iterations=1000, normalize=True)
+    ck = cugraph.katz_centrality(G, tol=1e-6, max_iter=1000)
+    assert ck["katz_centrality"].dtype == torch.float32
+    assert np.abs(_scores(ck, "katz_centrality", 34) - want).max() <= 1e-5
+    pr_want, _ = util.oracle_pagerank(s, d, None, 34, dtype=np.float64, alpha=0.85, epsilon=1e-12,
+                                      max_iterations=1000)
+    pr = cugraph.pagerank(G, tol=1e-7, max_iter=1000)
+    assert np.abs(_scores(pr, "pagerank", 34) - pr_want).max() <= 1e-5
+
+
+def test_warnings_and_errors(cugraph):
+    src, dst, w = _karate()
+    G = cugraph.Graph(directed=True)
+    G.from_cudf_edgelist({"src": src, "dst": dst, "weights": w}, source="src", destination="dst",
+                         edge_attr="weights")
+    with pytest.warns(UserWarning, match="Pagerank expects the 'store_transposed' flag"):
+        df = cugraph.pagerank(G)
+    assert abs(float(df["pagerank"].sum()) - 1.0) < 1e-4
+    G = cugraph.Graph(directed=True)
+    G.from_cudf_edgelist({"src": src, "dst": dst, "weights": w}, source="src", destination="dst",
+                         edge_attr="weights", store_transposed=True)
+    with pytest.warns(UserWarning, match="of type: float64"):
+        cugraph.pagerank(G, personalization=pd.DataFrame({"vertex": [17, 26],
+                                                          "values": [0.5, 0.75]}))
+    with pytest.raises(ValueError):  # the library rejects a vertex that is not in the graph
+        cugraph.pagerank(G, personalization={"vertex": np.array([77], np.int32),
+                                             "values": np.array([1.0], np.float32)})
