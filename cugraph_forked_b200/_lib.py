@@ -119,6 +119,21 @@ class HitsParams(ctypes.Structure):
     ]
 
 
+class HostEdgelistInfo(ctypes.Structure):
+    _fields_ = [
+        ("num_rows", ctypes.c_int64),
+        ("num_cols", ctypes.c_int64),
+        ("num_edges", ctypes.c_int64),
+        ("file_entries", ctypes.c_int64),
+        ("is_symmetric", ctypes.c_int32),
+        ("is_pattern", ctypes.c_int32),
+        ("vertex_type", ctypes.c_int32),
+        ("weight_type", ctypes.c_int32),
+        ("pinned", ctypes.c_int32),
+        ("pad", ctypes.c_int32),
+    ]
+
+
 # every symbol include/b200_cugraph.h declares: name -> (restype, argtypes)
 _vp, _sz, _i, _d, _u64 = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_double, ctypes.c_uint64
 _pp = ctypes.POINTER(ctypes.c_void_p)
@@ -149,6 +164,13 @@ SIGNATURES = {
                        ctypes.POINTER(CentralityStats)]),
     "b200_generate_rmat_edgelist": (_i, [_vp, _i, _sz, _d, _d, _d, _u64, _i, _u64, _i, _vp, _vp]),
     "b200_uniform_fill": (_i, [_vp, _i, _vp, _sz, _u64]),
+    "b200_read_matrix_market": (_i, [ctypes.c_char_p, _i, _i, _i, _pp]),
+    "b200_read_csv_edgelist": (_i, [ctypes.c_char_p, ctypes.c_char, _i, _i, _i, _i, _pp]),
+    "b200_host_edgelist_info": (_i, [_vp, ctypes.POINTER(HostEdgelistInfo)]),
+    "b200_host_edgelist_src": (_vp, [_vp]),
+    "b200_host_edgelist_dst": (_vp, [_vp]),
+    "b200_host_edgelist_weights": (_vp, [_vp]),
+    "b200_host_edgelist_free": (None, [_vp]),
     "b200_build_info": (ctypes.c_char_p, []),
 }
 

@@ -1,0 +1,508 @@
+// Edge-list ingest (include/b200_cugraph.h, "Edge-list ingest"): Matrix-Market and delimited
+// text files -> COO in page-locked host memory.  Host code only; the device enters when the
+// caller copies the arrays and calls b200_graph_create_sg.
+//
+// Replaces the per-entry fscanf loop of cpp/tests/utilities/matrix_market_file_utilities.cu
+// (mm_properties :53-116, mm_to_coo :133-222, read_edgelist_from_matrix_market_file :266-322)
+// with: the file mapped read-only, a split at line boundaries over the host threads, a
+// from_chars parse into per-thread vectors, and a copy into the final arrays at the prefix
+// offsets - so entry order (and the mirrored entry right after each off-diagonal entry of a
+// symmetric file, :199-215) is the reference's whatever the thread count.
+#include <algorithm>
+#include <charconv>
+#include <chrono>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <cuda_runtime.h>
+
+#include "../../include/b200_cugraph.h"
+#include "common.cuh"
+
+struct b200_host_edgelist {
+  b200_host_edgelist_info_t info{};
+  void* src{nullptr};
+  void* dst{nullptr};
+  void* weights{nullptr};
+  bool pinned_src{false}, pinned_dst{false}, pinned_weights{false};
+};
+
+namespace b200 {
+namespace {
+
+// the file, mapped read-only: the parser threads read the page cache directly
+struct file_bytes {
+  const char* ptr{nullptr};
+  size_t len{0};
+  explicit file_bytes(const char* path)
+  {
+    B200_EXPECTS(path != nullptr, kInvalidInput, "path is NULL");
+    int fd = open(path, O_RDONLY);
+    B200_EXPECTS(fd >= 0, kInvalidInput, std::string("fopen (") + path + ") failure.");
+    struct stat st {};
+    bool ok = fstat(fd, &st) == 0 && S_ISREG(st.st_mode);
+    if (ok && st.st_size > 0) {
+      void* m = mmap(nullptr, static_cast<size_t>(st.st_size), PROT_READ, MAP_PRIVATE, fd, 0);
+      ok      = m != MAP_FAILED;
+      if (ok) {
+        ptr = static_cast<const char*>(m);
+        len = static_cast<size_t>(st.st_size);
+        (void)madvise(m, len, MADV_SEQUENTIAL);
+      }
+    }
+    close(fd);
+    B200_EXPECTS(ok, kInvalidInput, std::string("could not read ") + path);
+  }
+  ~file_bytes()
+  {
+    if (ptr) munmap(const_cast<char*>(ptr), len);
+  }
+  file_bytes(file_bytes const&)            = delete;
+  file_bytes& operator=(file_bytes const&) = delete;
+  const char* begin() const { return ptr ? ptr : ""; }
+  const char* end() const { return begin() + len; }
+};
+
+inline bool is_space(char c) { return c == ' ' || c == '\t' || c == '\r' || c == '\v' || c == '\f'; }
+
+// end of the line starting at p (position of '\n' or end)
+inline const char* line_end(const char* p, const char* end)
+{
+  const void* nl = memchr(p, '\n', static_cast<size_t>(end - p));
+  return nl ? static_cast<const char*>(nl) : end;
+}
+
+inline const char* skip_spaces(const char* p, const char* e)
+{
+  while (p < e && is_space(*p)) ++p;
+  return p;
+}
+
+inline bool blank(const char* p, const char* e) { return skip_spaces(p, e) == e; }
+
+template <typename T>
+inline bool parse_number(const char*& p, const char* e, T& out)
+{
+  p = skip_spaces(p, e);
+  if (p < e && *p == '+') ++p;  // from_chars takes no leading '+', fscanf does
+  auto r = std::from_chars(p, e, out);
+  if (r.ec != std::errc()) return false;
+  p = r.ptr;
+  return true;
+}
+
+// vertex ids: plain decimal digits, the common case, without the from_chars call
+inline bool parse_id(const char*& p, const char* e, int64_t& out)
+{
+  p = skip_spaces(p, e);
+  const char* q = p;
+  if (q < e && *q == '+') ++q;
+  uint64_t v       = 0;
+  const char* d0   = q;
+  while (q < e && static_cast<unsigned>(*q - '0') <= 9u && q - d0 < 18) v = v * 10 + static_cast<unsigned>(*q++ - '0');
+  if (q == d0 || (q < e && static_cast<unsigned>(*q - '0') <= 9u)) return parse_number(p, e, out);  // sign, overflow, junk
+  out = static_cast<int64_t>(v);
+  p   = q;
+  return true;
+}
+
+struct parse_options {
+  bool mtx{false};       // 1-based ids; mirrored entries when `mirror`
+  bool mirror{false};
+  bool skew{false};
+  bool has_values{false};   // a value column is expected in the file
+  bool want_values{false};  // ... and kept
+  char delimiter{' '};
+};
+
+struct chunk_out {
+  std::vector<int64_t> src, dst;
+  std::vector<double> val;
+  int64_t file_entries{0};
+  int64_t max_id{-1};
+  std::string err;
+};
+
+// one field separator of a delimited file: the delimiter itself, surrounded by optional blanks
+// (a blank delimiter therefore means "any run of blanks", which is what fscanf's ' ' does)
+inline void skip_delimiter(const char*& p, const char* e, char delim)
+{
+  p = skip_spaces(p, e);
+  if (!is_space(delim) && p < e && *p == delim) ++p;
+}
+
+void parse_chunk(const char* begin, const char* end, int64_t first_line, parse_options const& o,
+                 chunk_out& out)
+{
+  int64_t line_no = first_line;
+  // room for one entry per 12 bytes of text (grows if the lines are shorter), twice when mirrored
+  size_t guess = static_cast<size_t>(end - begin) / 12 * (o.mirror ? 2 : 1) + 16;
+  out.src.reserve(guess);
+  out.dst.reserve(guess);
+  if (o.want_values) out.val.reserve(guess);
+  for (const char* p = begin; p < end; ++line_no) {
+    const char* e    = line_end(p, end);
+    const char* next = e < end ? e + 1 : end;
+    if (blank(p, e) || (o.mtx && *skip_spaces(p, e) == '%')) {
+      p = next;
+      continue;
+    }
+    int64_t r{}, c{};
+    double v     = 1.0;
+    const char* q = p;
+    bool ok       = parse_id(q, e, r);
+    if (ok) {
+      skip_delimiter(q, e, o.delimiter);
+      ok = parse_id(q, e, c);
+    }
+    if (ok && o.has_values) {
+      skip_delimiter(q, e, o.delimiter);
+      ok = parse_number(q, e, v);
+    }
+    if (!ok) {
+      out.err = "could not read matrix data (line " + std::to_string(line_no + 1) + ")";
+      return;
+    }
+    if (o.mtx) {
+      --r;
+      --c;
+    }
+    if (r < 0 || c < 0) {
+      out.err = "negative vertex id (line " + std::to_string(line_no + 1) + ")";
+      return;
+    }
+    out.max_id = std::max(out.max_id, std::max(r, c));
+    ++out.file_entries;
+    out.src.push_back(r);
+    out.dst.push_back(c);
+    if (o.want_values) out.val.push_back(v);
+    if (o.mirror && r != c) {
+      out.src.push_back(c);
+      out.dst.push_back(r);
+      if (o.want_values) out.val.push_back(o.skew ? -v : v);
+    }
+    p = next;
+  }
+}
+
+void* host_alloc(size_t bytes, bool& pinned)
+{
+  void* p = nullptr;
+  if (posix_memalign(&p, 4096, std::max<size_t>(bytes, 4096)) != 0 || p == nullptr)
+    throw error(kAllocError, "host allocation failed");
+  // page-lock when a device is there; a host without one (the CPU test-suite) keeps pageable memory
+  pinned = cudaHostRegister(p, std::max<size_t>(bytes, 4096), cudaHostRegisterDefault) == cudaSuccess;
+  if (!pinned) (void)cudaGetLastError();
+  return p;
+}
+
+template <typename T>
+void narrow(std::vector<chunk_out> const& parts, std::vector<int64_t> const& offsets, int which,
+            void* dst_array, unsigned threads)
+{
+  auto work = [&](size_t i) {
+    T* d = static_cast<T*>(dst_array) + offsets[i];
+    if (which == 2) {
+      auto const& s = parts[i].val;
+      for (size_t k = 0; k < s.size(); ++k) d[k] = static_cast<T>(s[k]);
+    } else {
+      auto const& s = which == 0 ? parts[i].src : parts[i].dst;
+      for (size_t k = 0; k < s.size(); ++k) d[k] = static_cast<T>(s[k]);
+    }
+  };
+  std::vector<std::thread> pool;
+  for (unsigned t = 1; t < threads; ++t)
+    pool.emplace_back([&, t] {
+      for (size_t i = t; i < parts.size(); i += threads) work(i);
+    });
+  for (size_t i = 0; i < parts.size(); i += threads) work(i);
+  for (auto& th : pool) th.join();
+}
+
+b200_host_edgelist* parse_body(const char* begin, const char* end, int64_t first_line,
+                               parse_options const& o, int vertex_type, int weight_type,
+                               int threads_arg)
+{
+  unsigned hw      = std::max(1u, std::thread::hardware_concurrency());
+  size_t bytes     = static_cast<size_t>(end - begin);
+  // an explicit thread count is honoured (tests use it on small files); the default is one
+  // thread per 64 KB of text up to the hardware threads
+  unsigned threads = threads_arg > 0 ? std::min(static_cast<unsigned>(threads_arg), 1024u)
+                                     : static_cast<unsigned>(std::min<size_t>(hw, bytes / 65536 + 1));
+
+  // chunk starts, moved forward to the next line start
+  std::vector<const char*> cut(threads + 1, end);
+  cut[0] = begin;
+  for (unsigned t = 1; t < threads; ++t) {
+    const char* p = begin + bytes * t / threads;
+    if (p <= cut[t - 1]) {
+      cut[t] = cut[t - 1];
+      continue;
+    }
+    const char* e = line_end(p - 1, end);  // p - 1: a cut that falls on a line start stays there
+    cut[t]        = e < end ? e + 1 : end;
+  }
+  auto t0 = std::chrono::steady_clock::now();
+  std::vector<chunk_out> parts(threads);
+  {
+    std::vector<std::thread> pool;
+    for (unsigned t = 1; t < threads; ++t)
+      pool.emplace_back([&, t] { parse_chunk(cut[t], cut[t + 1], 0, o, parts[t]); });
+    parse_chunk(cut[0], cut[1], first_line, o, parts[0]);
+    for (auto& th : pool) th.join();
+  }
+  for (unsigned t = 0; t < threads; ++t) {
+    if (parts[t].err.empty()) continue;
+    if (t > 0) {
+      // recount the absolute line for the message
+      int64_t before = first_line + std::count(begin, cut[t], '\n');
+      chunk_out redo;
+      parse_chunk(cut[t], cut[t + 1], before, o, redo);
+      throw error(kInvalidInput, redo.err);
+    }
+    throw error(kInvalidInput, parts[t].err);
+  }
+
+  std::vector<int64_t> offsets(threads + 1, 0);
+  int64_t file_entries = 0, max_id = -1;
+  for (unsigned t = 0; t < threads; ++t) {
+    offsets[t + 1] = offsets[t] + static_cast<int64_t>(parts[t].src.size());
+    file_entries += parts[t].file_entries;
+    max_id = std::max(max_id, parts[t].max_id);
+  }
+  int64_t n = offsets[threads];
+  B200_EXPECTS(vertex_type == B200_INT64 || max_id <= INT32_MAX, kInvalidInput,
+               "vertex id does not fit vertex_type INT32");
+
+  auto t1 = std::chrono::steady_clock::now();
+  auto* el = new b200_host_edgelist{};
+  try {
+    size_t vsize      = vertex_type == B200_INT32 ? 4 : 8;
+    size_t wsize      = weight_type == B200_FLOAT32 ? 4 : 8;
+    el->src = host_alloc(static_cast<size_t>(n) * vsize, el->pinned_src);
+    el->dst = host_alloc(static_cast<size_t>(n) * vsize, el->pinned_dst);
+    if (o.want_values) el->weights = host_alloc(static_cast<size_t>(n) * wsize, el->pinned_weights);
+    if (vertex_type == B200_INT32) {
+      narrow<int32_t>(parts, offsets, 0, el->src, threads);
+      narrow<int32_t>(parts, offsets, 1, el->dst, threads);
+    } else {
+      narrow<int64_t>(parts, offsets, 0, el->src, threads);
+      narrow<int64_t>(parts, offsets, 1, el->dst, threads);
+    }
+    if (o.want_values) {
+      if (weight_type == B200_FLOAT32)
+        narrow<float>(parts, offsets, 2, el->weights, threads);
+      else
+        narrow<double>(parts, offsets, 2, el->weights, threads);
+    }
+    if (getenv("B200_INGEST_VERBOSE")) {
+      auto t2 = std::chrono::steady_clock::now();
+      fprintf(stderr, "[ingest] %u threads: parse %.1f ms, allocate + narrow %.1f ms, %lld edges\n",
+              threads, std::chrono::duration<double, std::milli>(t1 - t0).count(),
+              std::chrono::duration<double, std::milli>(t2 - t1).count(), static_cast<long long>(n));
+    }
+    el->info.num_edges    = n;
+    el->info.file_entries = file_entries;
+    el->info.num_rows     = max_id + 1;
+    el->info.num_cols     = max_id + 1;
+    el->info.vertex_type  = vertex_type;
+    el->info.weight_type  = o.want_values ? weight_type : -1;
+    el->info.pinned = el->pinned_src && el->pinned_dst && (!o.want_values || el->pinned_weights);
+  } catch (...) {
+    b200_host_edgelist_free(el);
+    throw;
+  }
+  return el;
+}
+
+std::string lower(std::string s)
+{
+  for (auto& c : s) c = static_cast<char>(tolower(static_cast<unsigned char>(c)));
+  return s;
+}
+
+std::vector<std::string> tokens(const char* p, const char* e)
+{
+  std::vector<std::string> out;
+  while (true) {
+    p = skip_spaces(p, e);
+    if (p >= e) break;
+    const char* q = p;
+    while (q < e && !is_space(*q)) ++q;
+    out.emplace_back(p, q);
+    p = q;
+  }
+  return out;
+}
+
+void check_types(int vertex_type, int weight_type, bool weights_optional)
+{
+  B200_EXPECTS(vertex_type == B200_INT32 || vertex_type == B200_INT64, kInvalidInput,
+               "vertex_type must be B200_INT32 or B200_INT64");
+  B200_EXPECTS(weight_type == B200_FLOAT32 || weight_type == B200_FLOAT64 ||
+                 (weights_optional && weight_type < 0),
+               kInvalidInput, "weight_type must be B200_FLOAT32 or B200_FLOAT64");
+}
+
+template <typename F>
+int guarded(F&& f)
+{
+  try {
+    f();
+    return kSuccess;
+  } catch (error const& e) {
+    set_last_error(e.what());
+    return e.code;
+  } catch (std::exception const& e) {
+    set_last_error(e.what());
+    return kUnknownError;
+  }
+}
+
+}  // namespace
+}  // namespace b200
+
+extern "C" {
+
+int b200_read_matrix_market(const char* path, int vertex_type, int weight_type, int threads,
+                            b200_host_edgelist_t** out)
+{
+  using namespace b200;
+  return guarded([&] {
+    B200_EXPECTS(out != nullptr, kInvalidInput, "out is NULL");
+    *out = nullptr;
+    check_types(vertex_type, weight_type, true);
+    file_bytes file(path);
+    const char* p   = file.begin();
+    const char* end = file.end();
+
+    // banner (mmio mm_read_banner): %%MatrixMarket matrix coordinate <field> <symmetry>
+    const char* e = line_end(p, end);
+    auto banner   = tokens(p, e);
+    B200_EXPECTS(banner.size() >= 5 && lower(banner[0]) == "%%matrixmarket", kInvalidInput,
+                 "could not read Matrix Market file properties.");
+    std::string object = lower(banner[1]), format = lower(banner[2]), field = lower(banner[3]),
+                symmetry = lower(banner[4]);
+    bool known_field = field == "pattern" || field == "real" || field == "integer" ||
+                       field == "complex";
+    bool known_sym   = symmetry == "general" || symmetry == "symmetric" ||
+                     symmetry == "skew-symmetric" || symmetry == "hermitian";
+    B200_EXPECTS(known_field && known_sym, kInvalidInput,
+                 "could not read Matrix Market file properties.");
+    // read_edgelist_from_matrix_market_file :289
+    B200_EXPECTS(object == "matrix" && format == "coordinate" && field != "complex" &&
+                   symmetry != "skew-symmetric",
+                 kInvalidInput, "invalid Matrix Market file properties.");
+    int64_t line_no = 1;
+    p               = e < end ? e + 1 : end;
+    // comments and blank lines, then the size line (mm_read_mtx_crd_size)
+    int64_t m = -1, n = -1, nnz = -1;
+    while (p < end) {
+      e = line_end(p, end);
+      if (!blank(p, e) && *skip_spaces(p, e) != '%') {
+        const char* q = p;
+        bool ok       = parse_number(q, e, m) && parse_number(q, e, n) && parse_number(q, e, nnz);
+        B200_EXPECTS(ok && m >= 0 && n >= 0 && nnz >= 0, kInvalidInput,
+                     "could not read Matrix Market file properties.");
+        p = e < end ? e + 1 : end;
+        ++line_no;
+        break;
+      }
+      p = e < end ? e + 1 : end;
+      ++line_no;
+    }
+    B200_EXPECTS(nnz >= 0, kInvalidInput, "could not read Matrix Market file properties.");
+
+    parse_options o;
+    o.mtx         = true;
+    o.mirror      = symmetry != "general";
+    o.has_values  = field != "pattern";
+    o.want_values = weight_type >= 0;
+    auto* el      = parse_body(p, end, line_no, o, vertex_type, weight_type < 0 ? B200_FLOAT32 : weight_type,
+                          threads);
+    if (el->info.file_entries != nnz || el->info.num_rows > std::max(m, n)) {
+      std::string msg = el->info.file_entries != nnz
+                          ? "could not read matrix data (" + std::to_string(el->info.file_entries) +
+                              " entries, size line says " + std::to_string(nnz) + ")"
+                          : "could not read matrix data (index beyond the size line)";
+      b200_host_edgelist_free(el);
+      throw error(kInvalidInput, msg);
+    }
+    el->info.num_rows     = m;
+    el->info.num_cols     = n;
+    el->info.is_symmetric = symmetry == "symmetric" ? 1 : 0;
+    el->info.is_pattern   = o.has_values ? 0 : 1;
+    *out                  = el;
+  });
+}
+
+int b200_read_csv_edgelist(const char* path, char delimiter, int skip_rows, int vertex_type,
+                           int weight_type, int threads, b200_host_edgelist_t** out)
+{
+  using namespace b200;
+  return guarded([&] {
+    B200_EXPECTS(out != nullptr, kInvalidInput, "out is NULL");
+    *out = nullptr;
+    check_types(vertex_type, weight_type, true);
+    B200_EXPECTS(skip_rows >= 0, kInvalidInput, "skip_rows must be >= 0");
+    B200_EXPECTS(delimiter != '\n' && delimiter != '\0' && delimiter != '.' && delimiter != '-' &&
+                   delimiter != '+' && !(delimiter >= '0' && delimiter <= '9'),
+                 kInvalidInput, "invalid delimiter");
+    file_bytes file(path);
+    const char* p   = file.begin();
+    const char* end = file.end();
+    int64_t line_no = 0;
+    for (; line_no < skip_rows && p < end; ++line_no) {
+      const char* e = line_end(p, end);
+      p             = e < end ? e + 1 : end;
+    }
+    parse_options o;
+    o.delimiter   = delimiter;
+    o.has_values  = weight_type >= 0;
+    o.want_values = weight_type >= 0;
+    *out = parse_body(p, end, line_no, o, vertex_type, weight_type < 0 ? B200_FLOAT32 : weight_type,
+                      threads);
+  });
+}
+
+int b200_host_edgelist_info(const b200_host_edgelist_t* e, b200_host_edgelist_info_t* out)
+{
+  if (e == nullptr || out == nullptr) {
+    b200::set_last_error("edge list or out is NULL");
+    return b200::kInvalidInput;
+  }
+  *out = e->info;
+  return b200::kSuccess;
+}
+
+const void* b200_host_edgelist_src(const b200_host_edgelist_t* e) { return e ? e->src : nullptr; }
+const void* b200_host_edgelist_dst(const b200_host_edgelist_t* e) { return e ? e->dst : nullptr; }
+const void* b200_host_edgelist_weights(const b200_host_edgelist_t* e)
+{
+  return e ? e->weights : nullptr;
+}
+
+void b200_host_edgelist_free(b200_host_edgelist_t* e)
+{
+  if (e == nullptr) return;
+  void* arrays[3] = {e->src, e->dst, e->weights};
+  bool pinned[3]  = {e->pinned_src, e->pinned_dst, e->pinned_weights};
+  for (int i = 0; i < 3; ++i) {
+    if (arrays[i] == nullptr) continue;
+    if (pinned[i]) (void)cudaHostUnregister(arrays[i]);
+    free(arrays[i]);
+  }
+  delete e;
+}
+
+}  // extern "C"

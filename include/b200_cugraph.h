@@ -221,6 +221,51 @@ int b200_generate_rmat_edgelist(b200_handle_t* h, int scale, size_t num_edges, d
 /* uniform [0,1) edge weights from the same generator (test_graphs.hpp:279-284) */
 int b200_uniform_fill(b200_handle_t* h, int value_type, void* out, size_t n, uint64_t seed);
 
+/* -------------------------------------------------------------------------------------------
+ * Edge-list ingest: the step before the path.  Host-side text -> COO in
+ * host memory that is page-locked when a device is present (ready for one cudaMemcpyAsync into
+ * b200_graph_create_sg).  No device work happens here.
+ *
+ * b200_read_matrix_market replaces read_edgelist_from_matrix_market_file / mm_properties /
+ * mm_to_coo (cpp/tests/utilities/matrix_market_file_utilities.cu:53-222, :266-322): coordinate
+ * files, pattern | real | integer values (complex and skew-symmetric are rejected as there,
+ * :289), 1-based -> 0-based ids, and for symmetric files the mirrored copy of every off-diagonal
+ * entry placed right after the entry (:199-215), so the edge order is the reference's.  Values
+ * are read as double and narrowed to weight_type, pattern entries are 1.0 (:174-178).
+ *
+ * b200_read_csv_edgelist replaces the cudf.read_csv(path, delimiter=' ', dtype=['int32',
+ * 'int32','float32'], header=None) call the reference's Python layer and datasets use
+ * (python/cugraph/cugraph/testing/utils.py read_csv_file, experimental/datasets/dataset.py):
+ * one edge per line, `src<delim>dst[<delim>weight]`, ids as written (no shift); the first
+ * skip_rows lines are dropped; weight_type < 0 ignores a third column; a missing third column
+ * with weight_type >= 0 is an error.
+ *
+ * The parse is split over `threads` host threads at line boundaries (0 = all hardware threads);
+ * the result does not depend on the thread count.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct b200_host_edgelist b200_host_edgelist_t;
+typedef struct b200_host_edgelist_info {
+  int64_t num_rows;      /* MTX size line (reference: number_of_vertices = rows); CSV: max id + 1 */
+  int64_t num_cols;
+  int64_t num_edges;     /* entries stored, mirrored copies included                            */
+  int64_t file_entries;  /* entries in the file                                                 */
+  int32_t is_symmetric;  /* MTX banner says symmetric (graph_properties_t::is_symmetric)         */
+  int32_t is_pattern;    /* no values in the file                                               */
+  int32_t vertex_type;   /* B200_INT32 | B200_INT64                                             */
+  int32_t weight_type;   /* B200_FLOAT32 | B200_FLOAT64, or -1: no weights array                */
+  int32_t pinned;        /* arrays are page-locked                                              */
+  int32_t pad;
+} b200_host_edgelist_info_t;
+int b200_read_matrix_market(const char* path, int vertex_type, int weight_type, int threads,
+                            b200_host_edgelist_t** out);
+int b200_read_csv_edgelist(const char* path, char delimiter, int skip_rows, int vertex_type,
+                           int weight_type, int threads, b200_host_edgelist_t** out);
+int b200_host_edgelist_info(const b200_host_edgelist_t* e, b200_host_edgelist_info_t* out);
+const void* b200_host_edgelist_src(const b200_host_edgelist_t* e);
+const void* b200_host_edgelist_dst(const b200_host_edgelist_t* e);
+const void* b200_host_edgelist_weights(const b200_host_edgelist_t* e); /* NULL if none */
+void b200_host_edgelist_free(b200_host_edgelist_t* e);
+
 /* library identification: "sm_100a" build tag + version */
 const char* b200_build_info(void);
 

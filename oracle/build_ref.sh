@@ -23,12 +23,17 @@ if [ -d "$ref/cpp/tests" ]; then
   sed -n '41,93p'  "$ref/cpp/tests/centrality/katz_centrality_test.cpp"        > "$tmp/ref_katz.inc"
   sed -n '41,96p'  "$ref/cpp/tests/centrality/eigenvector_centrality_test.cpp" > "$tmp/ref_eigenvector.inc"
   sed -n '46,127p' "$ref/cpp/tests/link_analysis/hits_test.cpp"                > "$tmp/ref_hits.inc"
+  sed -n '53,218p' "$ref/cpp/tests/utilities/matrix_market_file_utilities.cu"  > "$tmp/ref_mm.inc"
+  grep -q 'int mm_properties('                    "$tmp/ref_mm.inc"
+  grep -q 'int mm_to_coo('                        "$tmp/ref_mm.inc"
   grep -q 'hits_reference('                       "$tmp/ref_hits.inc"
   grep -q 'void pagerank_reference'               "$tmp/ref_pagerank.inc"
   grep -q 'void katz_centrality_reference'        "$tmp/ref_katz.inc"
   grep -q 'void eigenvector_centrality_reference' "$tmp/ref_eigenvector.inc"
   mkdir -p "$here/_ref"
-  $cxx $flags -I"$tmp" -o "$here/_ref/libcugraph_ref_oracle.so" "$here/ref_shim.cpp"
+  ${CC:-gcc} -O2 -fPIC -w -c "$ref/thirdparty/mmio/mmio.c" -o "$tmp/mmio.o"
+  $cxx $flags -I"$tmp" -I"$ref/thirdparty/mmio" -o "$here/_ref/libcugraph_ref_oracle.so" \
+    "$here/ref_shim.cpp" "$here/ref_mtx_shim.cpp" "$tmp/mmio.o"
   echo "built oracle/_ref/libcugraph_ref_oracle.so from $ref"
 else
   echo "reference tree not present; keeping prebuilt oracle/_ref (if any)"

@@ -182,3 +182,26 @@ def csc_from_coo(src, dst, weights, num_vertices):
     offsets = np.zeros(num_vertices + 1, dtype=np.int64)
     np.cumsum(np.bincount(dst, minlength=num_vertices), out=offsets[1:])
     return offsets, np.asarray(src)[order].astype(np.int32), None if weights is None else np.asarray(weights)[order]
+
+
+def read_mtx_ref(path, dtype=np.float32):
+    """The reference's own reader (mm_properties + mm_to_coo compiled in oracle/_ref), called as
+    read_edgelist_from_matrix_market_file does.  Returns (src, dst, weights, num_vertices,
+    is_symmetric, is_pattern)."""
+    lib = ref_lib()
+    m, k, nnz = ctypes.c_int64(), ctypes.c_int64(), ctypes.c_int64()
+    sym, pat = ctypes.c_int(), ctypes.c_int()
+    lib.ref_mtx_properties.restype = ctypes.c_long
+    rc = lib.ref_mtx_properties(os.fsencode(path), ctypes.byref(m), ctypes.byref(k),
+                                ctypes.byref(nnz), ctypes.byref(sym), ctypes.byref(pat))
+    if rc != 0:
+        raise RuntimeError({-1: "fopen failure", -2: "could not read Matrix Market file properties.",
+                            -3: "invalid Matrix Market file properties."}[rc])
+    rows = np.zeros(nnz.value, np.int32)
+    cols = np.zeros(nnz.value, np.int32)
+    vals = np.zeros(nnz.value, dtype)
+    fn = getattr(lib, "ref_mtx_to_coo_" + _sfx(dtype))
+    fn.restype = ctypes.c_long
+    if fn(os.fsencode(path), ctypes.c_int64(nnz.value), _p(rows), _p(cols), _p(vals)) != 0:
+        raise RuntimeError("could not read matrix data")
+    return rows, cols, vals, m.value, bool(sym.value), bool(pat.value)

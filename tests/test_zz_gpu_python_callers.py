@@ -134,7 +134,7 @@ def test_undirected_unweighted_graph(cugraph, oracle_built):
     assert np.abs(_scores(ck, "katz_centrality", 34) - want).max() <= 1e-5
     pr_want, _ = util.oracle_pagerank(s, d, None, 34, dtype=np.float64, alpha=0.85, epsilon=1e-12,
                                       max_iterations=1000)
-    pr = cugraph.pagerank(G, tol=1e-7, max_iter=1000)
+    pr = cugraph.pagerank(G, tol=1e-6, max_iter=1000)
     assert np.abs(_scores(pr, "pagerank", 34) - pr_want).max() <= 1e-5
 
 
@@ -155,3 +155,22 @@ def test_warnings_and_errors(cugraph):
     with pytest.raises(ValueError):  # the library rejects a vertex that is not in the graph
         cugraph.pagerank(G, personalization={"vertex": np.array([77], np.int32),
                                              "values": np.array([1.0], np.float32)})
+
+
+def test_matrix_market_file_to_pagerank(cugraph, oracle_built):
+    """File -> page-locked COO -> device columns -> Graph -> pagerank, the whole front of the path
+    (read_graph_from_matrix_market_file + cugraph.pagerank)."""
+    import os
+    from cugraph_forked_b200 import io
+    path = os.path.join(os.path.dirname(__file__), "golden", "netscience.mtx")
+    src, dst, w, info = io.read_matrix_market(path)
+    assert src.is_cuda and w.is_cuda and info.is_symmetric and info.num_edges == src.numel()
+    rs, rd, rw, nv, _ = util.load_mtx("netscience.mtx")
+    assert np.array_equal(src.cpu().numpy(), rs) and np.array_equal(w.cpu().numpy(), rw)
+    G = cugraph.Graph(directed=True)
+    G.from_cudf_edgelist({"src": src, "dst": dst, "w": w}, "src", "dst", "w", renumber=False,
+                         store_transposed=True)
+    df = cugraph.pagerank(G, tol=1e-6, max_iter=500)
+    want, _ = util.oracle_pagerank(rs, rd, rw, nv, dtype=np.float64, alpha=0.85, epsilon=1e-12,
+                                   max_iterations=1000)
+    assert np.abs(_scores(df, "pagerank", nv) - want).max() <= 1e-5
