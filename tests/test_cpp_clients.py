@@ -1,6 +1,7 @@
 """The C ABI from compiled clients: a pure-C program against include/cugraph_c (shaped like
 cpp/tests/c_api/pagerank_test.c) and a C++ program against the cugraph::pagerank /
-katz_centrality shims of include/cugraph_b200/algorithms.hpp.  Compiling and linking needs no
+katz_centrality / hits shims of include/cugraph_b200/algorithms.hpp (the hits client reads its
+graph through b200_read_matrix_market).  Compiling and linking needs no
 GPU (CPU suite); running them is a GPU test."""
 import os
 import subprocess
@@ -31,14 +32,15 @@ def _build(name):
     return exe
 
 
-@pytest.mark.parametrize("name", ["c_api_golden", "shim_golden"])
+@pytest.mark.parametrize("name", ["c_api_golden", "shim_golden", "hits_file_golden"])
 def test_clients_compile_and_link(name):
     assert os.path.exists(_build(name))
 
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("name,token", [("c_api_golden", "C_API_GOLDEN_OK"),
-                                        ("shim_golden", "SHIM_GOLDEN_OK")])
+                                        ("shim_golden", "SHIM_GOLDEN_OK"),
+                                        ("hits_file_golden", "HITS_FILE_GOLDEN_OK")])
 def test_clients_run(name, token):
     r = subprocess.run([_build(name)], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and token in r.stdout, (r.stdout, r.stderr)
