@@ -39,6 +39,18 @@ _DEVICE = "cuda"
 
 _MAX_SG_EDGES = 2147483100  # simpleGraph.py:161
 
+_handles = {}
+
+
+def _resource_handle():
+    """The reference makes a fresh `ResourceHandle()` for every graph and algorithm call; here one
+    is made on first use and shared, so that a graph and the calls on it run on the same library
+    stream and the library's per-handle workspace is kept between calls."""
+    key = _plc.__name__
+    if key not in _handles:
+        _handles[key] = _plc.ResourceHandle()
+    return _handles[key]
+
 
 # --------------------------------------------------------------------------------------------
 # Frame: the column table standing in for cudf.DataFrame
@@ -506,7 +518,7 @@ class Graph:
                                      is_symmetric=not self.graph_properties.directed)
         df = self.edgelist.edgelist_df
         self._plc_graph = _plc.SGGraph(
-            resource_handle=_plc.ResourceHandle(), graph_properties=props,
+            resource_handle=_resource_handle(), graph_properties=props,
             src_array=df["src"].contiguous(), dst_array=df["dst"].contiguous(),
             weight_array=None if weight_col is None else weight_col.contiguous(),
             edge_id_array=id_col, edge_type_array=type_col, store_transposed=store_transposed,
@@ -846,7 +858,7 @@ def pagerank(G, alpha=0.85, personalization=None, precomputed_vertex_out_weight=
             personalization = renumber_vertices(G, personalization)
         personalization = ensure_valid_dtype(G, personalization, "personalization")
         vertex, pagerank_values = _plc.personalized_pagerank(
-            resource_handle=_plc.ResourceHandle(), graph=G._plc_graph,
+            resource_handle=_resource_handle(), graph=G._plc_graph,
             precomputed_vertex_out_weight_vertices=pre_vtx_o_wgt_vertices,
             precomputed_vertex_out_weight_sums=pre_vtx_o_wgt_sums,
             personalization_vertices=_vertex_ids(G, personalization["vertex"]),
@@ -857,7 +869,7 @@ def pagerank(G, alpha=0.85, personalization=None, precomputed_vertex_out_weight=
             do_expensive_check=do_expensive_check)
     else:
         vertex, pagerank_values = _plc.pagerank(
-            resource_handle=_plc.ResourceHandle(), graph=G._plc_graph,
+            resource_handle=_resource_handle(), graph=G._plc_graph,
             precomputed_vertex_out_weight_vertices=pre_vtx_o_wgt_vertices,
             precomputed_vertex_out_weight_sums=pre_vtx_o_wgt_sums,
             initial_guess_vertices=initial_guess_vertices,
@@ -907,7 +919,7 @@ def katz_centrality(G, alpha=None, beta=1.0, max_iter=100, tol=1.0e-6, nstart=No
         betas = nstart[nstart.columns[0]].contiguous()
 
     vertices, values = _plc.katz_centrality(
-        resource_handle=_plc.ResourceHandle(), graph=G._plc_graph, betas=betas, alpha=alpha,
+        resource_handle=_resource_handle(), graph=G._plc_graph, betas=betas, alpha=alpha,
         beta=beta, epsilon=tol, max_iterations=max_iter, do_expensive_check=False)
 
     df = Frame()
@@ -929,7 +941,7 @@ def eigenvector_centrality(G, max_iter=100, tol=1.0e-6):
     _warn_not_transposed(G, "Eigenvector centrality")
 
     vertices, values = _plc.eigenvector_centrality(
-        resource_handle=_plc.ResourceHandle(), graph=G._plc_graph, epsilon=tol,
+        resource_handle=_resource_handle(), graph=G._plc_graph, epsilon=tol,
         max_iterations=max_iter, do_expensive_check=False)
 
     df = Frame()
@@ -956,7 +968,7 @@ def hits(G, max_iter=100, tol=1.0e-5, nstart=None, normalized=True):
         init_hubs_guess_values = nstart["values"].to(_edge_attr_dtype(G)).contiguous()
 
     vertices, hubs, authorities = _plc.hits(
-        resource_handle=_plc.ResourceHandle(), graph=G._plc_graph, tol=tol, max_iter=max_iter,
+        resource_handle=_resource_handle(), graph=G._plc_graph, tol=tol, max_iter=max_iter,
         initial_hubs_guess_vertices=init_hubs_guess_vertices,
         initial_hubs_guess_values=init_hubs_guess_values, normalized=normalized,
         do_expensive_check=False)
