@@ -799,9 +799,73 @@ def ensure_valid_dtype(input_graph, input_df, input_df_name):
     return input_df
 
 
+def _nx():
+    try:
+        import networkx
+    except ImportError:  # NetworkX is optional, as in the reference (utils.import_optional)
+        return None
+    return networkx
+
+
+def convert_from_nx(nxG, weight=None, do_renumber=True):
+    """utilities/nx_factory.py:76-106: NetworkX Graph / DiGraph -> Graph.  An unweighted graph
+    gives columns src, dst; a weighted one takes the edge attribute `weight`, or, when `weight`
+    is None, the single edge attribute the graph has (nx.to_pandas_edgelist), as float32
+    (:55).  The graph is stored transposed - the reference stores it untransposed here and then
+    warns about it in every centrality call on a NetworkX input."""
+    nx = _nx()
+    if isinstance(nxG, nx.classes.digraph.DiGraph):
+        G = Graph(directed=True)
+    elif isinstance(nxG, nx.classes.graph.Graph):
+        G = Graph()
+    else:
+        raise TypeError(f"nxG must be either a NetworkX Graph or DiGraph, got {type(nxG)}")
+    if nx.is_weighted(nxG) is False:
+        edges = list(nxG.edges(data=False))
+        df = {"src": _label_column([s for s, _ in edges]), "dst": _label_column([d for _, d in edges])}
+        G.from_cudf_edgelist(df, source="src", destination="dst", edge_attr=None,
+                             renumber=do_renumber, store_transposed=True)
+    elif weight is None:
+        pdf = nx.to_pandas_edgelist(nxG)
+        wt_col = [c for c in pdf.columns if c not in ("source", "target")]
+        if len(wt_col) != 1:
+            raise ValueError("Unable to determine weight column name")
+        pdf = pdf.rename(columns={wt_col[0]: "weight"})
+        G.from_cudf_edgelist(pdf, source="source", destination="target", edge_attr="weight",
+                             renumber=do_renumber, store_transposed=True)
+    else:
+        edges = list(nxG.edges(data=weight))
+        df = {"src": _label_column([s for s, _, _ in edges]),
+              "dst": _label_column([d for _, d, _ in edges]),
+              "weight": np.asarray([w for _, _, w in edges], dtype=np.float32)}
+        G.from_cudf_edgelist(df, source="src", destination="dst", edge_attr="weight",
+                             renumber=do_renumber, store_transposed=True)
+    return G
+
+
+def _label_column(values):
+    a = np.asarray(values)
+    return a.astype(np.int64) if a.dtype.kind in "iu" else a
+
+
+def ensure_cugraph_obj_for_nx(obj, nx_weight_attr="weight"):
+    """utilities/utils.py:326-341: (Graph, is_networkx_input)."""
+    nx = _nx()
+    if nx is not None and isinstance(obj, nx.Graph):
+        return convert_from_nx(obj, weight=nx_weight_attr), True
+    if isinstance(obj, Graph):
+        return obj, False
+    raise TypeError(f"input must be either a cuGraph or NetworkX graph type, got {type(obj)}")
+
+
+def df_score_to_dictionary(df, k, v="vertex"):
+    """utilities/nx_factory.py:109-137: {vertex: score}, ordered by vertex."""
+    df = df.sort_values(v)
+    keys = df[v].tolist()
+    return dict(zip(keys, df[k].tolist()))
+
+
 def _check_graph(G, name):
-    if not isinstance(G, Graph):
-        raise TypeError(f"{name}: G must be a Graph (NetworkX graphs are not supported here)")
     if G._plc_graph is None:
         raise RuntimeError("Graph is Empty")
 
@@ -823,10 +887,11 @@ def _vertex_ids(G, col):
 
 def pagerank(G, alpha=0.85, personalization=None, precomputed_vertex_out_weight=None,
              max_iter=100, tol=1.0e-5, nstart=None, weight=None, dangling=None):
-    """link_analysis/pagerank.py:61-244.  Returns a Frame with columns 'vertex' and 'pagerank'.
-    `personalization` / `nstart`: tables with 'vertex' and 'values';
-    `precomputed_vertex_out_weight`: 'vertex' and 'sums'.  `weight` and `dangling` exist for
-    NetworkX compatibility and are ignored, as in the reference."""
+    """link_analysis/pagerank.py:61-244.  Returns a Frame with columns 'vertex' and 'pagerank'
+    (a {vertex: score} dict when G is a NetworkX graph).  `personalization` / `nstart`: tables
+    with 'vertex' and 'values'; `precomputed_vertex_out_weight`: 'vertex' and 'sums'.  `weight`
+    names the edge attribute of a NetworkX input; `dangling` is ignored, as in the reference."""
+    G, isNx = ensure_cugraph_obj_for_nx(G, weight)
     _check_graph(G, "pagerank")
     _warn_not_transposed(G, "Pagerank")
     initial_guess_vertices = initial_guess_values = None
@@ -882,6 +947,8 @@ def pagerank(G, alpha=0.85, personalization=None, precomputed_vertex_out_weight=
     df["pagerank"] = pagerank_values
     if G.renumbered:
         df = G.unrenumber(df, "vertex")
+    if isNx is True:
+        df = df_score_to_dictionary(df, "pagerank")
     return df
 
 
@@ -891,6 +958,7 @@ def katz_centrality(G, alpha=None, beta=1.0, max_iter=100, tol=1.0e-6, nstart=No
     alpha=None uses 1 / (largest degree).  As in the reference, `normalized` is accepted and
     not forwarded, and `nstart` travels in the C API's `betas` slot, which the library accepts
     and does not use (c_api/katz.cpp:158)."""
+    G, isNx = ensure_cugraph_obj_for_nx(G)
     _check_graph(G, "katz_centrality")
     _warn_not_transposed(G, "Katz centrality")
 
@@ -927,6 +995,8 @@ def katz_centrality(G, alpha=None, beta=1.0, max_iter=100, tol=1.0e-6, nstart=No
     df["katz_centrality"] = values
     if G.renumbered:
         df = G.unrenumber(df, "vertex")
+    if isNx is True:
+        return df_score_to_dictionary(df, "katz_centrality")
     return df
 
 
@@ -937,6 +1007,7 @@ def eigenvector_centrality(G, max_iter=100, tol=1.0e-6):
         raise ValueError(f"'max_iter' must be a positive integer, got: {max_iter}")
     if (not isinstance(tol, float)) or (tol <= 0.0):
         raise ValueError(f"'tol' must be a positive float, got: {tol}")
+    G, isNx = ensure_cugraph_obj_for_nx(G)
     _check_graph(G, "eigenvector_centrality")
     _warn_not_transposed(G, "Eigenvector centrality")
 
@@ -949,6 +1020,8 @@ def eigenvector_centrality(G, max_iter=100, tol=1.0e-6):
     df["eigenvector_centrality"] = values
     if G.renumbered:
         df = G.unrenumber(df, "vertex")
+    if isNx is True:
+        return df_score_to_dictionary(df, "eigenvector_centrality")
     return df
 
 
@@ -957,6 +1030,7 @@ def hits(G, max_iter=100, tol=1.0e-5, nstart=None, normalized=True):
     `nstart`: table with 'vertex' and 'values', the starting hub scores.  The reference hands
     nstart['vertex'] to the library as is; with a label-renumbered graph the labels are
     translated first, which the reference leaves undone (and would fail on)."""
+    G, isNx = ensure_cugraph_obj_for_nx(G)
     _check_graph(G, "hits")
     _warn_not_transposed(G, "HITS")
     init_hubs_guess_vertices = init_hubs_guess_values = None
@@ -979,4 +1053,7 @@ def hits(G, max_iter=100, tol=1.0e-5, nstart=None, normalized=True):
     results["authorities"] = authorities
     if G.renumbered:
         results = G.unrenumber(results, "vertex")
+    if isNx is True:
+        results = (df_score_to_dictionary(results, "hubs"),
+                   df_score_to_dictionary(results, "authorities"))
     return results

@@ -398,7 +398,7 @@ def test_transposed_false_warnings(cugraph):
 def test_algorithms_need_a_loaded_graph(cugraph):
     with pytest.raises(RuntimeError, match="Graph is Empty"):
         cugraph.pagerank(cugraph.Graph(directed=True))
-    with pytest.raises(TypeError, match="must be a Graph"):
+    with pytest.raises(TypeError, match="input must be either a cuGraph or NetworkX graph"):
         cugraph.pagerank({"not": "a graph"})
 
 

@@ -174,3 +174,26 @@ def test_matrix_market_file_to_pagerank(cugraph, oracle_built):
     want, _ = util.oracle_pagerank(rs, rd, rw, nv, dtype=np.float64, alpha=0.85, epsilon=1e-12,
                                    max_iterations=1000)
     assert np.abs(_scores(df, "pagerank", nv) - want).max() <= 1e-5
+
+
+# ---- the reference's cuGraph-vs-NetworkX tests (tests/nx_cases.py) on the CUDA library --------
+
+@pytest.mark.parametrize("name", ["karate.mtx", "netscience.mtx"])
+@pytest.mark.parametrize("personalization_perc,has_guess,has_precomputed",
+                         [(0, 0, 0), (10, 1, 1), (50, 0, 1)])
+def test_pagerank_vs_networkx(cugraph, name, personalization_perc, has_guess, has_precomputed):
+    from tests import nx_cases
+    nx_cases.pagerank_case(cugraph, name, personalization_perc, has_guess, has_precomputed)
+
+
+@pytest.mark.parametrize("name", ["karate.mtx", "dolphins.mtx", "netscience.mtx"])
+def test_centralities_vs_networkx(cugraph, name):
+    from tests import nx_cases
+    nx_cases.katz_case(cugraph, name)
+    nx_cases.eigenvector_case(cugraph, name)
+    nx_cases.hits_case(cugraph, name)
+
+
+def test_networkx_graph_inputs(cugraph):
+    from tests import nx_cases
+    nx_cases.nx_input_case(cugraph)
