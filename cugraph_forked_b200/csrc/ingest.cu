@@ -26,80 +26,11 @@
 
 #include <cuda_runtime.h>
 
-#include "../../include/b200_cugraph.h"
-#include "common.cuh"
-
-struct b200_host_edgelist {
-  b200_host_edgelist_info_t info{};
-  void* src{nullptr};
-  void* dst{nullptr};
-  void* weights{nullptr};
-  bool pinned_src{false}, pinned_dst{false}, pinned_weights{false};
-};
+#include "ingest.cuh"
 
 namespace b200 {
+namespace ingest {
 namespace {
-
-// the file, mapped read-only: the parser threads read the page cache directly
-struct file_bytes {
-  const char* ptr{nullptr};
-  size_t len{0};
-  explicit file_bytes(const char* path)
-  {
-    B200_EXPECTS(path != nullptr, kInvalidInput, "path is NULL");
-    int fd = open(path, O_RDONLY);
-    B200_EXPECTS(fd >= 0, kInvalidInput, std::string("fopen (") + path + ") failure.");
-    struct stat st {};
-    bool ok = fstat(fd, &st) == 0 && S_ISREG(st.st_mode);
-    if (ok && st.st_size > 0) {
-      void* m = mmap(nullptr, static_cast<size_t>(st.st_size), PROT_READ, MAP_PRIVATE, fd, 0);
-      ok      = m != MAP_FAILED;
-      if (ok) {
-        ptr = static_cast<const char*>(m);
-        len = static_cast<size_t>(st.st_size);
-        (void)madvise(m, len, MADV_SEQUENTIAL);
-      }
-    }
-    close(fd);
-    B200_EXPECTS(ok, kInvalidInput, std::string("could not read ") + path);
-  }
-  ~file_bytes()
-  {
-    if (ptr) munmap(const_cast<char*>(ptr), len);
-  }
-  file_bytes(file_bytes const&)            = delete;
-  file_bytes& operator=(file_bytes const&) = delete;
-  const char* begin() const { return ptr ? ptr : ""; }
-  const char* end() const { return begin() + len; }
-};
-
-inline bool is_space(char c) { return c == ' ' || c == '\t' || c == '\r' || c == '\v' || c == '\f'; }
-
-// end of the line starting at p (position of '\n' or end)
-inline const char* line_end(const char* p, const char* end)
-{
-  const void* nl = memchr(p, '\n', static_cast<size_t>(end - p));
-  return nl ? static_cast<const char*>(nl) : end;
-}
-
-inline const char* skip_spaces(const char* p, const char* e)
-{
-  while (p < e && is_space(*p)) ++p;
-  return p;
-}
-
-inline bool blank(const char* p, const char* e) { return skip_spaces(p, e) == e; }
-
-template <typename T>
-inline bool parse_number(const char*& p, const char* e, T& out)
-{
-  p = skip_spaces(p, e);
-  if (p < e && *p == '+') ++p;  // from_chars takes no leading '+', fscanf does
-  auto r = std::from_chars(p, e, out);
-  if (r.ec != std::errc()) return false;
-  p = r.ptr;
-  return true;
-}
 
 // vertex ids: plain decimal digits, the common case, without the from_chars call
 inline bool parse_id(const char*& p, const char* e, int64_t& out)
@@ -115,15 +46,6 @@ inline bool parse_id(const char*& p, const char* e, int64_t& out)
   p   = q;
   return true;
 }
-
-struct parse_options {
-  bool mtx{false};       // 1-based ids; mirrored entries when `mirror`
-  bool mirror{false};
-  bool skew{false};
-  bool has_values{false};   // a value column is expected in the file
-  bool want_values{false};  // ... and kept
-  char delimiter{' '};
-};
 
 struct chunk_out {
   std::vector<int64_t> src, dst;
@@ -193,17 +115,6 @@ void parse_chunk(const char* begin, const char* end, int64_t first_line, parse_o
     }
     p = next;
   }
-}
-
-void* host_alloc(size_t bytes, bool& pinned)
-{
-  void* p = nullptr;
-  if (posix_memalign(&p, 4096, std::max<size_t>(bytes, 4096)) != 0 || p == nullptr)
-    throw error(kAllocError, "host allocation failed");
-  // page-lock when a device is there; a host without one (the CPU test-suite) keeps pageable memory
-  pinned = cudaHostRegister(p, std::max<size_t>(bytes, 4096), cudaHostRegisterDefault) == cudaSuccess;
-  if (!pinned) (void)cudaGetLastError();
-  return p;
 }
 
 template <typename T>
@@ -325,51 +236,8 @@ b200_host_edgelist* parse_body(const char* begin, const char* end, int64_t first
   return el;
 }
 
-std::string lower(std::string s)
-{
-  for (auto& c : s) c = static_cast<char>(tolower(static_cast<unsigned char>(c)));
-  return s;
-}
-
-std::vector<std::string> tokens(const char* p, const char* e)
-{
-  std::vector<std::string> out;
-  while (true) {
-    p = skip_spaces(p, e);
-    if (p >= e) break;
-    const char* q = p;
-    while (q < e && !is_space(*q)) ++q;
-    out.emplace_back(p, q);
-    p = q;
-  }
-  return out;
-}
-
-void check_types(int vertex_type, int weight_type, bool weights_optional)
-{
-  B200_EXPECTS(vertex_type == B200_INT32 || vertex_type == B200_INT64, kInvalidInput,
-               "vertex_type must be B200_INT32 or B200_INT64");
-  B200_EXPECTS(weight_type == B200_FLOAT32 || weight_type == B200_FLOAT64 ||
-                 (weights_optional && weight_type < 0),
-               kInvalidInput, "weight_type must be B200_FLOAT32 or B200_FLOAT64");
-}
-
-template <typename F>
-int guarded(F&& f)
-{
-  try {
-    f();
-    return kSuccess;
-  } catch (error const& e) {
-    set_last_error(e.what());
-    return e.code;
-  } catch (std::exception const& e) {
-    set_last_error(e.what());
-    return kUnknownError;
-  }
-}
-
 }  // namespace
+}  // namespace ingest
 }  // namespace b200
 
 extern "C" {
@@ -378,70 +246,30 @@ int b200_read_matrix_market(const char* path, int vertex_type, int weight_type, 
                             b200_host_edgelist_t** out)
 {
   using namespace b200;
+  using namespace b200::ingest;
   return guarded([&] {
     B200_EXPECTS(out != nullptr, kInvalidInput, "out is NULL");
     *out = nullptr;
     check_types(vertex_type, weight_type, true);
     file_bytes file(path);
-    const char* p   = file.begin();
-    const char* end = file.end();
-
-    // banner (mmio mm_read_banner): %%MatrixMarket matrix coordinate <field> <symmetry>
-    const char* e = line_end(p, end);
-    auto banner   = tokens(p, e);
-    B200_EXPECTS(banner.size() >= 5 && lower(banner[0]) == "%%matrixmarket", kInvalidInput,
-                 "could not read Matrix Market file properties.");
-    std::string object = lower(banner[1]), format = lower(banner[2]), field = lower(banner[3]),
-                symmetry = lower(banner[4]);
-    bool known_field = field == "pattern" || field == "real" || field == "integer" ||
-                       field == "complex";
-    bool known_sym   = symmetry == "general" || symmetry == "symmetric" ||
-                     symmetry == "skew-symmetric" || symmetry == "hermitian";
-    B200_EXPECTS(known_field && known_sym, kInvalidInput,
-                 "could not read Matrix Market file properties.");
-    // read_edgelist_from_matrix_market_file :289
-    B200_EXPECTS(object == "matrix" && format == "coordinate" && field != "complex" &&
-                   symmetry != "skew-symmetric",
-                 kInvalidInput, "invalid Matrix Market file properties.");
-    int64_t line_no = 1;
-    p               = e < end ? e + 1 : end;
-    // comments and blank lines, then the size line (mm_read_mtx_crd_size)
-    int64_t m = -1, n = -1, nnz = -1;
-    while (p < end) {
-      e = line_end(p, end);
-      if (!blank(p, e) && *skip_spaces(p, e) != '%') {
-        const char* q = p;
-        bool ok       = parse_number(q, e, m) && parse_number(q, e, n) && parse_number(q, e, nnz);
-        B200_EXPECTS(ok && m >= 0 && n >= 0 && nnz >= 0, kInvalidInput,
-                     "could not read Matrix Market file properties.");
-        p = e < end ? e + 1 : end;
-        ++line_no;
-        break;
-      }
-      p = e < end ? e + 1 : end;
-      ++line_no;
-    }
-    B200_EXPECTS(nnz >= 0, kInvalidInput, "could not read Matrix Market file properties.");
-
+    mtx_header h = read_mtx_header(file);
     parse_options o;
     o.mtx         = true;
-    o.mirror      = symmetry != "general";
-    o.has_values  = field != "pattern";
+    o.mirror      = h.mirror;
+    o.has_values  = !h.pattern;
     o.want_values = weight_type >= 0;
-    auto* el      = parse_body(p, end, line_no, o, vertex_type, weight_type < 0 ? B200_FLOAT32 : weight_type,
-                          threads);
-    if (el->info.file_entries != nnz || el->info.num_rows > std::max(m, n)) {
-      std::string msg = el->info.file_entries != nnz
-                          ? "could not read matrix data (" + std::to_string(el->info.file_entries) +
-                              " entries, size line says " + std::to_string(nnz) + ")"
-                          : "could not read matrix data (index beyond the size line)";
+    auto* el = parse_body(h.body, file.end(), h.body_line, o, vertex_type,
+                          weight_type < 0 ? B200_FLOAT32 : weight_type, threads);
+    try {
+      check_mtx_counts(h, el->info.file_entries, el->info.num_rows - 1);
+    } catch (...) {
       b200_host_edgelist_free(el);
-      throw error(kInvalidInput, msg);
+      throw;
     }
-    el->info.num_rows     = m;
-    el->info.num_cols     = n;
-    el->info.is_symmetric = symmetry == "symmetric" ? 1 : 0;
-    el->info.is_pattern   = o.has_values ? 0 : 1;
+    el->info.num_rows     = h.rows;
+    el->info.num_cols     = h.cols;
+    el->info.is_symmetric = h.symmetric ? 1 : 0;
+    el->info.is_pattern   = h.pattern ? 1 : 0;
     *out                  = el;
   });
 }
@@ -450,28 +278,22 @@ int b200_read_csv_edgelist(const char* path, char delimiter, int skip_rows, int 
                            int weight_type, int threads, b200_host_edgelist_t** out)
 {
   using namespace b200;
+  using namespace b200::ingest;
   return guarded([&] {
     B200_EXPECTS(out != nullptr, kInvalidInput, "out is NULL");
     *out = nullptr;
     check_types(vertex_type, weight_type, true);
     B200_EXPECTS(skip_rows >= 0, kInvalidInput, "skip_rows must be >= 0");
-    B200_EXPECTS(delimiter != '\n' && delimiter != '\0' && delimiter != '.' && delimiter != '-' &&
-                   delimiter != '+' && !(delimiter >= '0' && delimiter <= '9'),
-                 kInvalidInput, "invalid delimiter");
+    check_delimiter(delimiter);
     file_bytes file(path);
-    const char* p   = file.begin();
-    const char* end = file.end();
     int64_t line_no = 0;
-    for (; line_no < skip_rows && p < end; ++line_no) {
-      const char* e = line_end(p, end);
-      p             = e < end ? e + 1 : end;
-    }
+    const char* p   = csv_body(file, skip_rows, line_no);
     parse_options o;
     o.delimiter   = delimiter;
     o.has_values  = weight_type >= 0;
     o.want_values = weight_type >= 0;
-    *out = parse_body(p, end, line_no, o, vertex_type, weight_type < 0 ? B200_FLOAT32 : weight_type,
-                      threads);
+    *out = parse_body(p, file.end(), line_no, o, vertex_type,
+                      weight_type < 0 ? B200_FLOAT32 : weight_type, threads);
   });
 }
 
