@@ -130,7 +130,7 @@ class HostEdgelistInfo(ctypes.Structure):
         ("vertex_type", ctypes.c_int32),
         ("weight_type", ctypes.c_int32),
         ("pinned", ctypes.c_int32),
-        ("pad", ctypes.c_int32),
+        ("parser", ctypes.c_int32),
     ]
 
 
@@ -171,6 +171,13 @@ SIGNATURES = {
     "b200_host_edgelist_dst": (_vp, [_vp]),
     "b200_host_edgelist_weights": (_vp, [_vp]),
     "b200_host_edgelist_free": (None, [_vp]),
+    "b200_read_matrix_market_device": (_i, [_vp, ctypes.c_char_p, _i, _i, _pp]),
+    "b200_read_csv_edgelist_device": (_i, [_vp, ctypes.c_char_p, ctypes.c_char, _i, _i, _i, _pp]),
+    "b200_device_edgelist_info": (_i, [_vp, ctypes.POINTER(HostEdgelistInfo)]),
+    "b200_device_edgelist_src": (_vp, [_vp]),
+    "b200_device_edgelist_dst": (_vp, [_vp]),
+    "b200_device_edgelist_weights": (_vp, [_vp]),
+    "b200_device_edgelist_free": (None, [_vp]),
     "b200_build_info": (ctypes.c_char_p, []),
 }
 

@@ -140,6 +140,8 @@ void narrow(std::vector<chunk_out> const& parts, std::vector<int64_t> const& off
   for (auto& th : pool) th.join();
 }
 
+}  // namespace
+
 b200_host_edgelist* parse_body(const char* begin, const char* end, int64_t first_line,
                                parse_options const& o, int vertex_type, int weight_type,
                                int threads_arg)
@@ -236,7 +238,6 @@ b200_host_edgelist* parse_body(const char* begin, const char* end, int64_t first
   return el;
 }
 
-}  // namespace
 }  // namespace ingest
 }  // namespace b200
 

@@ -237,6 +237,11 @@ inline const char* csv_body(file_bytes const& file, int skip_rows, int64_t& line
   return p;
 }
 
+// the host parser (ingest.cu): text [begin, end) -> COO in host memory, `threads_arg` host threads
+b200_host_edgelist* parse_body(const char* begin, const char* end, int64_t first_line,
+                               parse_options const& o, int vertex_type, int weight_type,
+                               int threads_arg);
+
 // the size-line checks of a parsed Matrix-Market body (stricter than the reference's fscanf loop)
 inline void check_mtx_counts(mtx_header const& h, int64_t file_entries, int64_t max_id)
 {

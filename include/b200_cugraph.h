@@ -254,7 +254,7 @@ typedef struct b200_host_edgelist_info {
   int32_t vertex_type;   /* B200_INT32 | B200_INT64                                             */
   int32_t weight_type;   /* B200_FLOAT32 | B200_FLOAT64, or -1: no weights array                */
   int32_t pinned;        /* arrays are page-locked                                              */
-  int32_t pad;
+  int32_t parser;        /* 0: parsed by the host reader, 1: by the device kernels              */
 } b200_host_edgelist_info_t;
 int b200_read_matrix_market(const char* path, int vertex_type, int weight_type, int threads,
                             b200_host_edgelist_t** out);
@@ -265,6 +265,24 @@ const void* b200_host_edgelist_src(const b200_host_edgelist_t* e);
 const void* b200_host_edgelist_dst(const b200_host_edgelist_t* e);
 const void* b200_host_edgelist_weights(const b200_host_edgelist_t* e); /* NULL if none */
 void b200_host_edgelist_free(b200_host_edgelist_t* e);
+
+/* The same two readers with the parse on the GPU: the text is copied to HBM once and parsed
+ * there (one CTA per 65 KB tile staged through shared memory, one thread per 260-byte chunk;
+ * count - scan - write), the COO arrays are left in device memory on h's device, ready for
+ * b200_graph_create_sg.  Same files accepted, same arrays (order, ids, correctly rounded
+ * values) and same errors as the host readers: whatever the kernels flag - a malformed line, a
+ * line over 1 KB - is handed to the host reader.  info.pinned is 0. */
+typedef struct b200_device_edgelist b200_device_edgelist_t;
+int b200_read_matrix_market_device(b200_handle_t* h, const char* path, int vertex_type,
+                                   int weight_type, b200_device_edgelist_t** out);
+int b200_read_csv_edgelist_device(b200_handle_t* h, const char* path, char delimiter,
+                                  int skip_rows, int vertex_type, int weight_type,
+                                  b200_device_edgelist_t** out);
+int b200_device_edgelist_info(const b200_device_edgelist_t* e, b200_host_edgelist_info_t* out);
+const void* b200_device_edgelist_src(const b200_device_edgelist_t* e);
+const void* b200_device_edgelist_dst(const b200_device_edgelist_t* e);
+const void* b200_device_edgelist_weights(const b200_device_edgelist_t* e); /* NULL if none */
+void b200_device_edgelist_free(b200_device_edgelist_t* e);
 
 /* library identification: "sm_100a" build tag + version */
 const char* b200_build_info(void);
