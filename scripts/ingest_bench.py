@@ -40,3 +40,21 @@ with tempfile.TemporaryDirectory(dir=os.environ.get("INGEST_TMP")) as d:
             np.array_equal(got[0].numpy(), ref[0]) and np.array_equal(got[2].numpy(), ref[2]))
         print(f"library reader, threads={t or 'all'}: {dt:.3f} s  {n / dt / 1e6:.2f} M entries/s  "
               f"{size / dt / 1e6:.0f} MB/s  identical={ok}")
+    if torch.cuda.is_available():
+        # host reader + upload vs the device parser (B200_INGEST_VERBOSE=1 prints its phases)
+        from cugraph_forked_b200 import engine
+        h = engine.Handle()
+        for parser in ("host", "device"):
+            io.read_matrix_market(path, parser=parser, handle=h) if parser == "device" else \
+                io.read_matrix_market(path)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            got = io.read_matrix_market(path, parser=parser, handle=h) if parser == "device" else \
+                io.read_matrix_market(path)
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            ok = (not cpu_oracle.ref_available()) or (
+                np.array_equal(got[0].cpu().numpy(), ref[0]) and
+                np.array_equal(got[2].cpu().numpy(), ref[2]))
+            print(f"file -> device columns, parser={parser} ({got[3].parser}): {dt:.3f} s  "
+                  f"{n / dt / 1e6:.2f} M entries/s  {size / dt / 1e6:.0f} MB/s  identical={ok}")
