@@ -45,10 +45,9 @@ def _column(ptr, n, np_dtype, device):
         return torch.empty(0, dtype=torch.from_numpy(np.empty(0, np_dtype)).dtype, device=device)
     nbytes = n * np.dtype(np_dtype).itemsize
     host = np.frombuffer((ctypes.c_char * nbytes).from_address(ptr), dtype=np_dtype)
-    t = torch.from_numpy(host)
     if device == "cpu":
-        return t.clone()
-    out = t.to(device)
+        return torch.from_numpy(host.copy())
+    out = torch.from_numpy(host).to(device)
     torch.cuda.current_stream().synchronize()  # the host arrays are freed right after
     return out
 
