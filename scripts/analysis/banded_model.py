@@ -281,3 +281,161 @@ def spmv_banded(L, x, dtype=np.float64, minc=3, kernel=1, le=16):
     if prod.size:
         y[nz] = np.add.reduceat(prod, roff[:-1][nz])
     return y
+
+
+# ---------------------------------------------------------------------------------------------
+# Round-2 layout: a row's direct edges become "global cells", so that
+# phase 2 is a streaming segmented sum over partials only.  Model of the layout and of both
+# phases; not implemented in CUDA yet.
+# ---------------------------------------------------------------------------------------------
+
+def add_global_cells(L, off, idx, w, cellmax=2048, window=2048):
+    """On top of build_layout: every edge that is NOT pre-reduced goes, in CSC order, into the
+    global stream `gidx` (32-bit source | cell start << 31, weights in `gw`).  A global cell is a
+    run of one row's direct edges, cut where the stream position is a multiple of `cellmax`
+    (every task window of `window` >= cellmax stream positions then starts at most one cell late).
+    A row's partial slots are consecutive: first its banded cells in CSC order, then its global
+    cells in stream order; `poff[r] .. poff[r + 1]` delimits them, `ppos` (band-major rank ->
+    slot) is renumbered accordingly and `gpos` maps the global cell rank to its slot."""
+    off = np.asarray(off, np.int64)
+    idx = np.asarray(idx, np.int64)
+    ne = idx.size
+    nrows = off.size - 1
+    banded, f = L["banded"], L["f"]
+    row = np.repeat(np.arange(nrows), np.diff(off))
+    direct = ~banded
+    ge = np.flatnonzero(direct)                    # CSC positions of the stream's edges
+    grow = row[ge]
+    gstart = np.ones(ge.size, bool)
+    gstart[1:] = grow[1:] != grow[:-1]
+    gstart |= (np.arange(ge.size) % cellmax) == 0
+    gidx = (idx[ge] | (gstart.astype(np.int64) << 31)).astype(np.uint32)
+    gw = None if w is None else w[ge]
+    head = banded & f                              # banded cell starts, CSC order
+    n_bcells = np.bincount(row[head], minlength=nrows)
+    n_gcells = np.bincount(grow[gstart], minlength=nrows)
+    poff = np.concatenate(([0], np.cumsum(n_bcells + n_gcells)))
+    # slot of each banded cell: poff[row] + its rank among the row's banded cells
+    hpos = np.flatnonzero(head)
+    hrow = row[hpos]
+    first_of_row = np.concatenate(([0], np.cumsum(n_bcells)))[hrow]
+    slot_b = poff[hrow] + (np.arange(hpos.size) - first_of_row)
+    # ppos is indexed by band-major cell rank; L["ppos"] holds the OLD slot = CSC-order cell rank
+    ppos = slot_b[L["ppos"]]
+    gcell_row = grow[gstart]
+    gfirst = np.concatenate(([0], np.cumsum(n_gcells)))[gcell_row]
+    gpos = poff[gcell_row] + n_bcells[gcell_row] + (np.arange(gcell_row.size) - gfirst)
+    # tasks over the global stream, as for a band: the cells that START inside a window
+    starts = np.flatnonzero(gstart)
+    gtasks = []
+    for lo in range(0, ge.size, window):
+        hi = min(lo + window, ge.size)
+        a = int(np.searchsorted(starts, lo))
+        b = int(np.searchsorted(starts, hi))
+        first = int(starts[a]) if a < starts.size else ge.size
+        end = int(starts[b]) if b < starts.size else ge.size
+        gtasks.append(dict(first=first, rank_first=a, count=max(end - first, 0), band=0))
+    G = dict(L)
+    G.update(ppos=ppos, gidx=gidx, gw=gw, gpos=gpos, gtasks=gtasks, poff=poff,
+             n_slots=int(poff[-1]), n_global=int(ge.size))
+    return G
+
+
+def spmv_global_cells(G, x, dtype=np.float64, le=16):
+    """Phase 1: band tasks (band_reduce2 lane algorithm, shared-memory gathers) and global tasks
+    (the same lane algorithm with 32-bit indices and global gathers) fill `pval`; phase 2 is
+    y[r] = sum(pval[poff[r]:poff[r + 1]])."""
+    pval = np.full(G["n_slots"], np.nan, dtype)
+    for t in G["tasks"]:
+        run_task2(G, t, x, pval, dtype, le)
+    # the global stream through the same routine: a "band" of 2^31 entries at offset 0
+    S = dict(bits=31, bidx=G["gidx"], bw=G["gw"], ppos=G["gpos"])
+    for t in G["gtasks"]:
+        _run_task2_wide(S, t, x, pval, dtype, le)
+    assert not np.isnan(pval).any(), "a partial was never written"
+    poff = G["poff"]
+    y = np.zeros(poff.size - 1, dtype)
+    nz = poff[:-1] < poff[1:]
+    y[nz] = np.add.reduceat(pval, poff[:-1][nz])
+    return y
+
+
+def _run_task2_wide(S, t, x, pval, dtype, le):
+    """run_task2 with the cell-start flag in bit 31 of a 32-bit index (global cells)."""
+    wide = dict(S)
+    flags = (S["bidx"] >> 31).astype(bool)
+    # re-express the stream in run_task2's terms: 15-bit-style flag at 0x8000 is too narrow for
+    # 31-bit sources, so run the lane algorithm on (source, flag) pairs directly
+    src = (S["bidx"] & 0x7FFFFFFF).astype(np.int64)
+    a0 = t["first"] & ~7
+    lead = t["first"] - a0
+    total = lead + t["count"]
+    se = 32 * le
+    steps = (total + se - 1) // se
+    pp = t["rank_first"]
+    rank = 0
+    carry = dtype(0)
+    ppos, bw = wide["ppos"], wide["bw"]
+
+    def store(slot, val):
+        assert np.isnan(pval[slot]), "partial written twice"
+        pval[slot] = val
+
+    for st in range(steps):
+        fm = [0] * 32
+        scratch = [[dtype(0)] * le for _ in range(32)]
+        tails = [dtype(0)] * 32
+        for lane in range(32):
+            base = st * se + lane * le
+            run = dtype(0)
+            for i in range(le):
+                pos = a0 + base + i
+                valid = lead <= base + i < total
+                v = dtype(0)
+                flag = False
+                if valid:
+                    v = dtype(x[src[pos]])
+                    if bw is not None:
+                        v = dtype(v * bw[pos])
+                    flag = bool(flags[pos])
+                scratch[lane][i] = run
+                if flag:
+                    fm[lane] |= 1 << i
+                    run = dtype(0)
+                run = dtype(run + v)
+            tails[lane] = run
+        cnt = [bin(m).count("1") for m in fm]
+        step_flags = sum(cnt)
+        fl = sum((cnt[l] > 0) << l for l in range(32))
+        sv = list(tails)
+        seg0 = []
+        for lane in range(32):
+            le_m = fl & ((1 << (lane + 1)) - 1)
+            seg0.append(le_m.bit_length() - 1 if le_m else 0)
+        o = 1
+        while o < 32:
+            pv = [sv[l - o] if l >= o else dtype(0) for l in range(32)]
+            for l in range(32):
+                if l - o >= seg0[l]:
+                    sv[l] = dtype(sv[l] + pv[l])
+            o <<= 1
+        for lane in range(32):
+            lt = (1 << lane) - 1
+            carry_in = carry
+            if lane > 0:
+                carry_in = sv[lane - 1] if (fl & lt) else dtype(sv[lane - 1] + carry)
+            r = rank + sum(cnt[:lane]) - 1
+            m = fm[lane]
+            add = carry_in
+            while m:
+                i = (m & -m).bit_length() - 1
+                m &= m - 1
+                val = dtype(scratch[lane][i] + add)
+                add = dtype(0)
+                if r >= 0:
+                    store(int(ppos[pp + r]), val)
+                r += 1
+        carry = sv[31] if fl else dtype(sv[31] + carry)
+        rank += step_flags
+    if rank > 0:
+        store(int(ppos[pp + rank - 1]), carry)

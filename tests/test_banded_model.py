@@ -73,3 +73,38 @@ def test_float32_error_small():
     nz = off[:-1] < off[1:]
     ref[nz] = np.add.reduceat(x[idx].astype(np.float64), off[:-1][nz])
     assert np.max(np.abs(y - ref) / np.maximum(ref, 1e-30)) < 2e-6
+
+
+@pytest.mark.parametrize("bits,cellmax,window,hot_min,weighted", [
+    (6, 64, 64, 16, False),
+    (6, 32, 64, 1, True),
+    (8, 2048, 2048, 64, False),
+    (5, 24, 40, 1, True),
+])
+def test_global_cells_layout_equals_plain_spmv(bits, cellmax, window, hot_min, weighted):
+    """The round-2 layout: direct edges as global cells, phase 2 a
+    streaming segmented sum over partials only."""
+    nv, off, idx = _csc(10, 16, seed=7)
+    rng = np.random.default_rng(3)
+    x = rng.random(nv)
+    w = rng.random(idx.size) if weighted else None
+    L = bm.build_layout(off, idx, w, nv, bits, cellmax=cellmax, window=window, hot_min=hot_min)
+    G = bm.add_global_cells(L, off, idx, w, cellmax=cellmax, window=window)
+    assert G["n_global"] + G["n_band"] == idx.size and G["n_global"] > 0
+    # a row's slots are consecutive and every slot belongs to exactly one cell
+    slots = np.concatenate([G["ppos"], G["gpos"]])
+    assert np.array_equal(np.sort(slots), np.arange(G["n_slots"]))
+    # every global task starts at a cell start and the tasks tile the stream
+    pos = 0
+    for t in G["gtasks"]:
+        if t["count"]:
+            assert t["first"] == pos and (int(G["gidx"][pos]) >> 31)
+            pos += t["count"]
+    assert pos == G["n_global"]
+    for le in (8, 16):
+        y = bm.spmv_global_cells(G, x, le=le)
+        prod = x[idx] * (w if weighted else 1.0)
+        ref = np.zeros(nv)
+        nz = off[:-1] < off[1:]
+        ref[nz] = np.add.reduceat(prod, off[:-1][nz])
+        assert np.allclose(y, ref, rtol=1e-12, atol=0)
