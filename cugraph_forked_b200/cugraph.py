@@ -467,7 +467,11 @@ class Graph:
         if values is not None:
             self.graph_properties.weights = True
         self.edgelist = _EdgeList(src, dst, None if values is None else values[0])
-        self._make_plc_graph(values, store_transposed, renumber)
+        try:
+            self._make_plc_graph(values, store_transposed, renumber)
+        except Exception:
+            self._reset()  # a graph the library refused holds no values
+            raise
 
     from_edgelist = from_cudf_edgelist
 
