@@ -27,6 +27,7 @@
 #include <cuda_runtime.h>
 
 #include "ingest.cuh"
+#include "ingest_gpu.cuh"
 
 namespace b200 {
 namespace ingest {
@@ -89,7 +90,13 @@ void parse_chunk(const char* begin, const char* end, int64_t first_line, parse_o
     }
     if (ok && o.has_values) {
       skip_delimiter(q, e, o.delimiter);
-      ok = parse_number(q, e, v);
+      // short decimals convert exactly with one multiplication or division (ingest_gpu.cuh);
+      // everything else goes through from_chars.  Both give the correctly rounded double.
+      const char* q2 = q;
+      if (gp_parse_value(q2, e, v) == 0)
+        q = q2;
+      else
+        ok = parse_number(q, e, v);
     }
     if (!ok) {
       out.err = "could not read matrix data (line " + std::to_string(line_no + 1) + ")";
