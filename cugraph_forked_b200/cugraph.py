@@ -475,6 +475,53 @@ class Graph:
 
     from_edgelist = from_cudf_edgelist
 
+    def from_cudf_adjlist(self, offset_col, index_col, value_col=None, renumber=True,
+                          store_transposed=False):
+        """graph_classes.py:173: compressed-sparse-row input - `offset_col` [V + 1],
+        `index_col` [E] destinations, optional `value_col` [E].  The reference only stores the
+        arrays here (simpleGraph.py:365-370, a graph loaded this way cannot be handed to its
+        pylibcugraph algorithms); here the rows are expanded on the device and the graph is
+        built as from an edge list, so the centrality callers work on it."""
+        if self.edgelist is not None:
+            raise RuntimeError("Graph already has values")
+        offsets, indices = _column(offset_col), _column(index_col)
+        if not (_is_int_column(offsets) and _is_int_column(indices)):
+            raise ValueError("offset_col and index_col must be integer columns")
+        if offsets.numel() == 0 or int(offsets[-1]) != indices.numel() or int(offsets[0]) != 0:
+            raise ValueError("offset_col must run from 0 to len(index_col)")
+        degrees = offsets[1:] - offsets[:-1]
+        if bool((degrees < 0).any()):
+            raise ValueError("offset_col must be non-decreasing")
+        src = torch.repeat_interleave(
+            torch.arange(degrees.numel(), dtype=indices.dtype, device=indices.device),
+            degrees.to(torch.int64))
+        df = {"src": src, "dst": indices}
+        if value_col is not None:
+            df["weights"] = _column(value_col)
+        self.from_cudf_edgelist(df, "src", "dst", "weights" if value_col is not None else None,
+                                renumber=renumber, store_transposed=store_transposed)
+
+    def _compressed(self, by_destination):
+        df = self._need_edges()
+        major, minor = (df["dst"], df["src"]) if by_destination else (df["src"], df["dst"])
+        n = self.number_of_vertices()
+        order = torch.argsort(minor, stable=True)
+        order = order[torch.argsort(major[order], stable=True)]
+        counts = torch.bincount(major.to(torch.int64), minlength=n)
+        offsets = torch.zeros(n + 1, dtype=torch.int64, device=major.device)
+        offsets[1:] = torch.cumsum(counts, 0)
+        weights = df["weights"][order] if self.is_weighted() else None
+        return offsets.to(major.dtype), minor[order], weights
+
+    def view_adj_list(self):
+        """simpleGraph.py:372-414: (offsets, indices, weights) of the stored edge list by
+        source - internal ids, neighbours ascending; weights None for an unweighted graph."""
+        return self._compressed(False)
+
+    def view_transposed_adj_list(self):
+        """simpleGraph.py:416-465: the same by destination (the pull direction)."""
+        return self._compressed(True)
+
     def from_pandas_edgelist(self, pdf, source="source", destination="destination",
                              edge_attr=None, renumber=True, store_transposed=False):
         """graph_classes.py:295."""

@@ -221,6 +221,39 @@ def test_from_numpy_array(cugraph):
         cugraph.Graph().from_numpy_array([[0, 1], [1, 0]])
 
 
+def test_adjacency_list_round_trip(cugraph):
+    """graph_classes.py:173 from_cudf_adjlist and simpleGraph.py:372,416 view_(transposed_)adj_list
+    against scipy's CSR / CSC of the same matrix."""
+    import scipy.sparse as sp
+    src, dst, w = _karate()
+    M = sp.coo_matrix((w, (src, dst)), shape=(34, 34)).tocsr()
+    M.sort_indices()
+    G = cugraph.Graph(directed=True)
+    G.from_cudf_adjlist(M.indptr, M.indices, M.data, store_transposed=True)
+    assert G.number_of_edges() == len(src) and G.is_weighted()
+    off, ind, val = G.view_adj_list()
+    assert np.array_equal(off.numpy(), M.indptr) and np.array_equal(ind.numpy(), M.indices)
+    assert np.array_equal(val.numpy(), M.data)
+    T = M.tocsc()
+    T.sort_indices()
+    off, ind, val = G.view_transposed_adj_list()
+    assert np.array_equal(off.numpy(), T.indptr) and np.array_equal(ind.numpy(), T.indices)
+    assert np.array_equal(val.numpy(), T.data)
+    want, _ = util.oracle_pagerank(src, dst, w, 34, dtype=np.float32, alpha=0.85, epsilon=1e-6,
+                                   max_iterations=500)
+    got = _scores(cugraph.pagerank(G, tol=1e-6, max_iter=500), "pagerank", 34)
+    assert np.abs(got - want).max() <= 2e-6
+    U = cugraph.Graph(directed=True)
+    U.from_cudf_adjlist(M.indptr, M.indices)
+    assert not U.is_weighted() and U.view_adj_list()[2] is None
+    with pytest.raises(ValueError, match="run from 0 to len"):
+        cugraph.Graph().from_cudf_adjlist(M.indptr[:-1], M.indices)
+    with pytest.raises(ValueError, match="non-decreasing"):
+        cugraph.Graph().from_cudf_adjlist(np.array([0, 3, 2, 4]), np.array([1, 2, 0, 1]))
+    with pytest.raises(RuntimeError, match="already has values"):
+        G.from_cudf_adjlist(M.indptr, M.indices)
+
+
 # ---- pagerank ------------------------------------------------------------------------------
 
 def _toy(cugraph, store_transposed=True, dtype=np.float32):
