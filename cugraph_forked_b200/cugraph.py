@@ -396,19 +396,15 @@ class Graph:
         self.renumbered = False
         self.store_transposed = False
         self._plc_graph = None
+        self._handle = None
+        self.distributed = False
         self._node_count = None
         self._edge_count = None
 
     # ---- loading -------------------------------------------------------------------------
 
-    def from_cudf_edgelist(self, input_df, source="source", destination="destination",
-                           edge_attr=None, renumber=True, store_transposed=False,
-                           legacy_renum_only=False):
-        """graph_classes.py:95 / simpleGraph.py:110.  `input_df`: Frame, pandas.DataFrame or
-        dict of columns.  `source` / `destination` may be lists of column names (multi-column
-        vertex labels, which need renumber=True)."""
-        if self.edgelist is not None:
-            raise RuntimeError("Graph already has values")
+    def _edge_columns(self, input_df, source, destination, edge_attr):
+        """The column checks of simpleGraph.py:120-160, same messages."""
         if not (isinstance(input_df, (Frame, dict)) or hasattr(input_df, "columns")):
             raise TypeError("input should be a Frame, a pandas.DataFrame or a dict of columns")
         available = set(input_df.keys() if isinstance(input_df, dict) else input_df.columns)
@@ -432,6 +428,18 @@ class Graph:
         src_cols = [_column(input_df[c]) for c in s_col]
         dst_cols = [_column(input_df[c]) for c in d_col]
         values = None if attrs is None else [_column(input_df[c]) for c in attrs]
+        return s_col, d_col, src_cols, dst_cols, values
+
+    def from_cudf_edgelist(self, input_df, source="source", destination="destination",
+                           edge_attr=None, renumber=True, store_transposed=False,
+                           legacy_renum_only=False):
+        """graph_classes.py:95 / simpleGraph.py:110.  `input_df`: Frame, pandas.DataFrame or
+        dict of columns.  `source` / `destination` may be lists of column names (multi-column
+        vertex labels, which need renumber=True)."""
+        if self.edgelist is not None:
+            raise RuntimeError("Graph already has values")
+        s_col, d_col, src_cols, dst_cols, values = self._edge_columns(input_df, source,
+                                                                      destination, edge_attr)
         if int(src_cols[0].shape[0]) > _MAX_SG_EDGES:
             raise ValueError("edge list is too big to fit in a single GPU")
 
@@ -474,6 +482,58 @@ class Graph:
             raise
 
     from_edgelist = from_cudf_edgelist
+
+    def from_distributed_edgelist(self, input_df, source="source", destination="destination",
+                                  edge_attr=None, resource_handle=None, store_transposed=False,
+                                  num_global_edges=-1):
+        """The multi-GPU loader: what Graph.from_dask_cudf_edgelist (graph_classes.py:228,
+        simpleDistributedGraph.py) is to Dask, for one process per GPU.  Every rank calls it
+        with ITS slice of the edge list (any split) and a `pylibcugraph.ResourceHandle` made
+        from a multi-GPU engine handle; the library shuffles the edges to their 2D owners and
+        renumbers (MGGraph, graphs.pyx:300).  Integer single-column ids; an undirected graph
+        mirrors the local slice; parallel edges are kept as given (the reference's Dask
+        groupby de-duplicates across workers - pass a de-duplicated list).  The centrality
+        callers then return this rank's part of the result, and (vertex, value) inputs must
+        name vertices whose result rows this rank holds."""
+        if self.edgelist is not None:
+            raise RuntimeError("Graph already has values")
+        if resource_handle is None:
+            raise ValueError("from_distributed_edgelist needs the multi-GPU resource_handle")
+        s_col, d_col, src_cols, dst_cols, values = self._edge_columns(input_df, source,
+                                                                      destination, edge_attr)
+        if len(s_col) > 1 or not (_is_int_column(src_cols[0]) and _is_int_column(dst_cols[0])):
+            raise ValueError("the distributed loader takes single integer id columns")
+        if values is not None and len(values) != 1:
+            raise ValueError("the distributed loader takes one edge attribute (the weight)")
+        src, dst = src_cols[0], dst_cols[0]
+        if src.dtype != dst.dtype:
+            common = torch.promote_types(src.dtype, dst.dtype)
+            src, dst = src.to(common), dst.to(common)
+        weight = None if values is None else values[0]
+        if weight is not None and weight.dtype in (torch.int32, torch.int64):
+            weight = weight.to(torch.float32 if weight.dtype == torch.int32 else torch.float64)
+        if not self.graph_properties.directed:
+            off_diagonal = src != dst
+            src, dst = (torch.cat([src, dst[off_diagonal]]), torch.cat([dst, src[off_diagonal]]))
+            if weight is not None:
+                weight = torch.cat([weight, weight[off_diagonal]])
+        self.store_transposed = bool(store_transposed)
+        self.graph_properties.weights = weight is not None
+        self.edgelist = _EdgeList(src, dst, weight)
+        self.distributed = True
+        self._handle = resource_handle
+        props = _plc.GraphProperties(is_multigraph=True,
+                                     is_symmetric=not self.graph_properties.directed)
+        try:
+            self._plc_graph = _plc.MGGraph(
+                resource_handle=resource_handle, graph_properties=props,
+                src_array=src.contiguous(), dst_array=dst.contiguous(),
+                weight_array=None if weight is None else weight.contiguous(),
+                store_transposed=store_transposed, num_edges=num_global_edges,
+                do_expensive_check=False)
+        except Exception:
+            self._reset()
+            raise
 
     def from_cudf_adjlist(self, offset_col, index_col, value_col=None, renumber=True,
                           store_transposed=False):
@@ -568,8 +628,9 @@ class Graph:
         props = _plc.GraphProperties(is_multigraph=self.multi_edge,
                                      is_symmetric=not self.graph_properties.directed)
         df = self.edgelist.edgelist_df
+        self._handle = _resource_handle()
         self._plc_graph = _plc.SGGraph(
-            resource_handle=_resource_handle(), graph_properties=props,
+            resource_handle=self._handle, graph_properties=props,
             src_array=df["src"].contiguous(), dst_array=df["dst"].contiguous(),
             weight_array=None if weight_col is None else weight_col.contiguous(),
             edge_id_array=id_col, edge_type_array=type_col, store_transposed=store_transposed,
@@ -593,9 +654,11 @@ class Graph:
     def is_multigraph(self):
         return self.multi_edge
 
-    def _need_edges(self):
+    def _need_edges(self, local_ok=False):
         if self.edgelist is None:
             raise RuntimeError("Graph is Empty")
+        if self.distributed and not local_ok:
+            raise NotImplementedError("this rank holds only its slice of a distributed graph")
         return self.edgelist.edgelist_df
 
     def number_of_vertices(self):
@@ -974,7 +1037,7 @@ def pagerank(G, alpha=0.85, personalization=None, precomputed_vertex_out_weight=
             personalization = renumber_vertices(G, personalization)
         personalization = ensure_valid_dtype(G, personalization, "personalization")
         vertex, pagerank_values = _plc.personalized_pagerank(
-            resource_handle=_resource_handle(), graph=G._plc_graph,
+            resource_handle=G._handle, graph=G._plc_graph,
             precomputed_vertex_out_weight_vertices=pre_vtx_o_wgt_vertices,
             precomputed_vertex_out_weight_sums=pre_vtx_o_wgt_sums,
             personalization_vertices=_vertex_ids(G, personalization["vertex"]),
@@ -985,7 +1048,7 @@ def pagerank(G, alpha=0.85, personalization=None, precomputed_vertex_out_weight=
             do_expensive_check=do_expensive_check)
     else:
         vertex, pagerank_values = _plc.pagerank(
-            resource_handle=_resource_handle(), graph=G._plc_graph,
+            resource_handle=G._handle, graph=G._plc_graph,
             precomputed_vertex_out_weight_vertices=pre_vtx_o_wgt_vertices,
             precomputed_vertex_out_weight_sums=pre_vtx_o_wgt_sums,
             initial_guess_vertices=initial_guess_vertices,
@@ -1038,7 +1101,7 @@ def katz_centrality(G, alpha=None, beta=1.0, max_iter=100, tol=1.0e-6, nstart=No
         betas = nstart[nstart.columns[0]].contiguous()
 
     vertices, values = _plc.katz_centrality(
-        resource_handle=_resource_handle(), graph=G._plc_graph, betas=betas, alpha=alpha,
+        resource_handle=G._handle, graph=G._plc_graph, betas=betas, alpha=alpha,
         beta=beta, epsilon=tol, max_iterations=max_iter, do_expensive_check=False)
 
     df = Frame()
@@ -1063,7 +1126,7 @@ def eigenvector_centrality(G, max_iter=100, tol=1.0e-6):
     _warn_not_transposed(G, "Eigenvector centrality")
 
     vertices, values = _plc.eigenvector_centrality(
-        resource_handle=_resource_handle(), graph=G._plc_graph, epsilon=tol,
+        resource_handle=G._handle, graph=G._plc_graph, epsilon=tol,
         max_iterations=max_iter, do_expensive_check=False)
 
     df = Frame()
@@ -1093,7 +1156,7 @@ def hits(G, max_iter=100, tol=1.0e-5, nstart=None, normalized=True):
         init_hubs_guess_values = nstart["values"].to(_edge_attr_dtype(G)).contiguous()
 
     vertices, hubs, authorities = _plc.hits(
-        resource_handle=_resource_handle(), graph=G._plc_graph, tol=tol, max_iter=max_iter,
+        resource_handle=G._handle, graph=G._plc_graph, tol=tol, max_iter=max_iter,
         initial_hubs_guess_vertices=init_hubs_guess_vertices,
         initial_hubs_guess_values=init_hubs_guess_values, normalized=normalized,
         do_expensive_check=False)

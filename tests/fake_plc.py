@@ -133,3 +133,13 @@ def hits(resource_handle, graph, tol, max_iter, initial_hubs_guess_vertices,
     hubs, auth, _, _ = cpu_oracle.hits(offsets, indices, dtype=graph.dtype, max_iterations=max_iter,
                                        tolerance=tol, starting_hubs=start, normalize=normalized)
     return graph.result(hubs, auth)
+
+
+class MGGraph(SGGraph):
+    """World size 1 only: the whole edge list is this rank's slice; renumbered by the library."""
+
+    def __init__(self, resource_handle, graph_properties, src_array, dst_array, weight_array,
+                 store_transposed=False, num_edges=-1, do_expensive_check=False,
+                 edge_id_array=None, edge_type_array=None):
+        super().__init__(resource_handle, graph_properties, src_array, dst_array, weight_array,
+                         store_transposed=store_transposed, renumber=True)

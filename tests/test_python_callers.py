@@ -254,6 +254,39 @@ def test_adjacency_list_round_trip(cugraph):
         G.from_cudf_adjlist(M.indptr, M.indices)
 
 
+def test_distributed_loader_world_size_1(cugraph):
+    """from_distributed_edgelist (the from_dask_cudf_edgelist stand-in) with one rank holding
+    the whole list: same scores as the single-GPU loader; undirected slices are mirrored."""
+    src, dst, w = _karate()
+    rh = fake_plc.ResourceHandle()
+    G = cugraph.Graph(directed=True)
+    G.from_distributed_edgelist({"s": src, "d": dst, "w": w}, "s", "d", "w", resource_handle=rh,
+                                store_transposed=True, num_global_edges=len(src))
+    assert G.distributed and G._handle is rh
+    want, _ = util.oracle_pagerank(src, dst, w, 34, dtype=np.float32, alpha=0.85, epsilon=1e-6,
+                                   max_iterations=500)
+    got = _scores(cugraph.pagerank(G, tol=1e-6, max_iter=500), "pagerank", 34)
+    assert np.abs(got - want).max() <= 2e-6
+    with pytest.raises(NotImplementedError, match="only its slice"):
+        G.number_of_vertices()
+    with pytest.raises(NotImplementedError, match="only its slice"):
+        cugraph.katz_centrality(G)  # alpha=None needs the global degrees
+    kz = _scores(cugraph.katz_centrality(G, alpha=0.02, tol=1e-6, max_iter=500),
+                 "katz_centrality", 34)
+    kw, _ = util.oracle_katz(src, dst, w, 34, dtype=np.float32, alpha=0.02, beta=1.0, epsilon=1e-6,
+                             max_iterations=500, normalize=True)
+    assert np.abs(kz - kw).max() <= 1e-6
+    keep = src < dst
+    U = cugraph.Graph()
+    U.from_distributed_edgelist({"s": src[keep], "d": dst[keep]}, "s", "d", resource_handle=rh)
+    assert len(U.edgelist.edgelist_df) == 2 * int(keep.sum())
+    with pytest.raises(ValueError, match="needs the multi-GPU resource_handle"):
+        cugraph.Graph().from_distributed_edgelist({"s": src, "d": dst}, "s", "d")
+    with pytest.raises(ValueError, match="single integer id columns"):
+        cugraph.Graph().from_distributed_edgelist({"s": np.array(["a"]), "d": np.array(["b"])},
+                                                  "s", "d", resource_handle=rh)
+
+
 # ---- pagerank ------------------------------------------------------------------------------
 
 def _toy(cugraph, store_transposed=True, dtype=np.float32):

@@ -197,3 +197,33 @@ def test_centralities_vs_networkx(cugraph, name):
 def test_networkx_graph_inputs(cugraph):
     from tests import nx_cases
     nx_cases.nx_input_case(cugraph)
+
+
+def test_distributed_loader_world_size_1(cugraph, oracle_built):
+    """Graph.from_distributed_edgelist on a multi-GPU handle of world size 1 (every collective
+    degenerates, the whole MG path runs): same scores as the single-GPU loader."""
+    import os
+    from cugraph_forked_b200 import pylibcugraph as plc
+    from tests import mg_worker
+    os.environ.pop("WORLD_SIZE", None)
+    os.environ.pop("RANK", None)
+    handle, rank, world = mg_worker.make_handle()
+    assert (rank, world) == (0, 1)
+    rh = plc.ResourceHandle(handle)
+    src, dst, w = _karate()
+    G = cugraph.Graph(directed=True)
+    G.from_distributed_edgelist({"s": src, "d": dst, "w": w}, "s", "d", "w", resource_handle=rh,
+                                store_transposed=True, num_global_edges=len(src))
+    want, _ = util.oracle_pagerank(src, dst, w, 34, dtype=np.float64, alpha=0.85, epsilon=1e-12,
+                                   max_iterations=1000)
+    got = _scores(cugraph.pagerank(G, tol=1e-6, max_iter=500), "pagerank", 34)
+    assert np.abs(got - want).max() <= 1e-5
+    pv = np.array([3, 17], np.int32)
+    pw = np.array([0.5, 0.5], np.float32)
+    want, _ = util.oracle_pagerank(src, dst, w, 34, dtype=np.float64, alpha=0.85, epsilon=1e-12,
+                                   max_iterations=1000, personalization=(pv, pw))
+    got = _scores(cugraph.pagerank(G, tol=1e-6, max_iter=500,
+                                   personalization={"vertex": pv, "values": pw}), "pagerank", 34)
+    assert np.abs(got - want).max() <= 1e-5
+    with pytest.raises(NotImplementedError):
+        cugraph.hits(G)  # HITS is single-GPU in this round
