@@ -227,3 +227,12 @@ def test_distributed_loader_world_size_1(cugraph, oracle_built):
     assert np.abs(got - want).max() <= 1e-5
     with pytest.raises(NotImplementedError):
         cugraph.hits(G)  # HITS is single-GPU in this round
+
+
+def test_hits_file_client_runs():
+    """tests/cpp/hits_file_golden.cpp: b200_read_matrix_market -> cugraph::hits shim -> golden
+    vector of c_api/hits_test.c (compiled on the CPU by tests/test_cpp_clients.py)."""
+    import subprocess
+    from tests.test_cpp_clients import _build
+    r = subprocess.run([_build("hits_file_golden")], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "HITS_FILE_GOLDEN_OK" in r.stdout, (r.stdout, r.stderr)
