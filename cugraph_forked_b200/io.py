@@ -69,7 +69,7 @@ def _finish_device(el):
                 raw.__cuda_array_interface__ = {
                     "shape": (n,), "typestr": {torch.int32: "<i4", torch.int64: "<i8",
                                                torch.float32: "<f4", torch.float64: "<f8"}[dtype],
-                    "data": (ptr, True), "version": 2}
+                    "data": (ptr, False), "version": 2}
                 out.copy_(torch.as_tensor(raw, device="cuda"))
             return out
 
