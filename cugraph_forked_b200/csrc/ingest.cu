@@ -48,9 +48,12 @@ inline bool parse_id(const char*& p, const char* e, int64_t& out)
   return true;
 }
 
+// what one host thread parsed, already in the output types (an id that does not fit V is caught
+// through max_id before the arrays are used)
+template <typename V, typename W>
 struct chunk_out {
-  std::vector<int64_t> src, dst;
-  std::vector<double> val;
+  std::vector<V> src, dst;
+  std::vector<W> val;
   int64_t file_entries{0};
   int64_t max_id{-1};
   std::string err;
@@ -64,8 +67,9 @@ inline void skip_delimiter(const char*& p, const char* e, char delim)
   if (!is_space(delim) && p < e && *p == delim) ++p;
 }
 
+template <typename V, typename W>
 void parse_chunk(const char* begin, const char* end, int64_t first_line, parse_options const& o,
-                 chunk_out& out)
+                 chunk_out<V, W>& out)
 {
   int64_t line_no = first_line;
   // room for one entry per 12 bytes of text (grows if the lines are shorter), twice when mirrored
@@ -112,31 +116,27 @@ void parse_chunk(const char* begin, const char* end, int64_t first_line, parse_o
     }
     out.max_id = std::max(out.max_id, std::max(r, c));
     ++out.file_entries;
-    out.src.push_back(r);
-    out.dst.push_back(c);
-    if (o.want_values) out.val.push_back(v);
+    out.src.push_back(static_cast<V>(r));
+    out.dst.push_back(static_cast<V>(c));
+    if (o.want_values) out.val.push_back(static_cast<W>(v));
     if (o.mirror && r != c) {
-      out.src.push_back(c);
-      out.dst.push_back(r);
-      if (o.want_values) out.val.push_back(o.skew ? -v : v);
+      out.src.push_back(static_cast<V>(c));
+      out.dst.push_back(static_cast<V>(r));
+      if (o.want_values) out.val.push_back(static_cast<W>(o.skew ? -v : v));
     }
     p = next;
   }
 }
 
-template <typename T>
-void narrow(std::vector<chunk_out> const& parts, std::vector<int64_t> const& offsets, int which,
-            void* dst_array, unsigned threads)
+// the threads' pieces, copied side by side into the output array
+template <typename V, typename W, typename T>
+void concatenate(std::vector<chunk_out<V, W>> const& parts, std::vector<int64_t> const& offsets,
+                 std::vector<T> chunk_out<V, W>::*member, void* dst_array, unsigned threads)
 {
   auto work = [&](size_t i) {
-    T* d = static_cast<T*>(dst_array) + offsets[i];
-    if (which == 2) {
-      auto const& s = parts[i].val;
-      for (size_t k = 0; k < s.size(); ++k) d[k] = static_cast<T>(s[k]);
-    } else {
-      auto const& s = which == 0 ? parts[i].src : parts[i].dst;
-      for (size_t k = 0; k < s.size(); ++k) d[k] = static_cast<T>(s[k]);
-    }
+    auto const& piece = parts[i].*member;
+    if (!piece.empty())
+      memcpy(static_cast<T*>(dst_array) + offsets[i], piece.data(), piece.size() * sizeof(T));
   };
   std::vector<std::thread> pool;
   for (unsigned t = 1; t < threads; ++t)
@@ -147,11 +147,30 @@ void narrow(std::vector<chunk_out> const& parts, std::vector<int64_t> const& off
   for (auto& th : pool) th.join();
 }
 
+template <typename V, typename W>
+b200_host_edgelist* parse_body_t(const char* begin, const char* end, int64_t first_line,
+                                 parse_options const& o, int vertex_type, int weight_type,
+                                 int threads_arg);
+
 }  // namespace
 
 b200_host_edgelist* parse_body(const char* begin, const char* end, int64_t first_line,
                                parse_options const& o, int vertex_type, int weight_type,
                                int threads_arg)
+{
+  const bool v32 = vertex_type == B200_INT32, w32 = weight_type == B200_FLOAT32;
+  if (v32 && w32) return parse_body_t<int32_t, float>(begin, end, first_line, o, vertex_type, weight_type, threads_arg);
+  if (v32) return parse_body_t<int32_t, double>(begin, end, first_line, o, vertex_type, weight_type, threads_arg);
+  if (w32) return parse_body_t<int64_t, float>(begin, end, first_line, o, vertex_type, weight_type, threads_arg);
+  return parse_body_t<int64_t, double>(begin, end, first_line, o, vertex_type, weight_type, threads_arg);
+}
+
+namespace {
+
+template <typename V, typename W>
+b200_host_edgelist* parse_body_t(const char* begin, const char* end, int64_t first_line,
+                                 parse_options const& o, int vertex_type, int weight_type,
+                                 int threads_arg)
 {
   unsigned hw      = std::max(1u, std::thread::hardware_concurrency());
   size_t bytes     = static_cast<size_t>(end - begin);
@@ -173,7 +192,7 @@ b200_host_edgelist* parse_body(const char* begin, const char* end, int64_t first
     cut[t]        = e < end ? e + 1 : end;
   }
   auto t0 = std::chrono::steady_clock::now();
-  std::vector<chunk_out> parts(threads);
+  std::vector<chunk_out<V, W>> parts(threads);
   {
     std::vector<std::thread> pool;
     for (unsigned t = 1; t < threads; ++t)
@@ -186,7 +205,7 @@ b200_host_edgelist* parse_body(const char* begin, const char* end, int64_t first
     if (t > 0) {
       // recount the absolute line for the message
       int64_t before = first_line + std::count(begin, cut[t], '\n');
-      chunk_out redo;
+      chunk_out<V, W> redo;
       parse_chunk(cut[t], cut[t + 1], before, o, redo);
       throw error(kInvalidInput, redo.err);
     }
@@ -207,27 +226,15 @@ b200_host_edgelist* parse_body(const char* begin, const char* end, int64_t first
   auto t1 = std::chrono::steady_clock::now();
   auto* el = new b200_host_edgelist{};
   try {
-    size_t vsize      = vertex_type == B200_INT32 ? 4 : 8;
-    size_t wsize      = weight_type == B200_FLOAT32 ? 4 : 8;
-    el->src = host_alloc(static_cast<size_t>(n) * vsize, el->pinned_src);
-    el->dst = host_alloc(static_cast<size_t>(n) * vsize, el->pinned_dst);
-    if (o.want_values) el->weights = host_alloc(static_cast<size_t>(n) * wsize, el->pinned_weights);
-    if (vertex_type == B200_INT32) {
-      narrow<int32_t>(parts, offsets, 0, el->src, threads);
-      narrow<int32_t>(parts, offsets, 1, el->dst, threads);
-    } else {
-      narrow<int64_t>(parts, offsets, 0, el->src, threads);
-      narrow<int64_t>(parts, offsets, 1, el->dst, threads);
-    }
-    if (o.want_values) {
-      if (weight_type == B200_FLOAT32)
-        narrow<float>(parts, offsets, 2, el->weights, threads);
-      else
-        narrow<double>(parts, offsets, 2, el->weights, threads);
-    }
+    el->src = host_alloc(static_cast<size_t>(n) * sizeof(V), el->pinned_src);
+    el->dst = host_alloc(static_cast<size_t>(n) * sizeof(V), el->pinned_dst);
+    if (o.want_values) el->weights = host_alloc(static_cast<size_t>(n) * sizeof(W), el->pinned_weights);
+    concatenate(parts, offsets, &chunk_out<V, W>::src, el->src, threads);
+    concatenate(parts, offsets, &chunk_out<V, W>::dst, el->dst, threads);
+    if (o.want_values) concatenate(parts, offsets, &chunk_out<V, W>::val, el->weights, threads);
     if (getenv("B200_INGEST_VERBOSE")) {
       auto t2 = std::chrono::steady_clock::now();
-      fprintf(stderr, "[ingest] %u threads: parse %.1f ms, allocate + narrow %.1f ms, %lld edges\n",
+      fprintf(stderr, "[ingest] %u threads: parse %.1f ms, allocate + copy %.1f ms, %lld edges\n",
               threads, std::chrono::duration<double, std::milli>(t1 - t0).count(),
               std::chrono::duration<double, std::milli>(t2 - t1).count(), static_cast<long long>(n));
     }
@@ -244,6 +251,8 @@ b200_host_edgelist* parse_body(const char* begin, const char* end, int64_t first
   }
   return el;
 }
+
+}  // namespace
 
 }  // namespace ingest
 }  // namespace b200
