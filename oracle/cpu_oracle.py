@@ -205,3 +205,45 @@ def read_mtx_ref(path, dtype=np.float32):
     if fn(os.fsencode(path), ctypes.c_int64(nnz.value), _p(rows), _p(cols), _p(vals)) != 0:
         raise RuntimeError("could not read matrix data")
     return rows, cols, vals, m.value, bool(sym.value), bool(pat.value)
+
+
+def graph_ref(src, dst, weights, num_vertices, store_transposed=True):
+    """The reference's own host graph build (graph_reference, cpp/tests/structure/graph_test.cpp:
+    38-69, compiled in oracle/_ref): (offsets, indices, weights) with the neighbours of a row in
+    input order."""
+    lib = ref_lib()
+    src = np.ascontiguousarray(src, np.int32)
+    dst = np.ascontiguousarray(dst, np.int32)
+    w = None if weights is None else np.ascontiguousarray(weights, np.float64)
+    ne = len(src)
+    offsets = np.zeros(num_vertices + 1, np.int64)
+    indices = np.zeros(ne, np.int32)
+    out_w = np.zeros(ne if w is not None else 0, np.float64)
+    lib.ref_graph_i32_f64.restype = ctypes.c_long
+    lib.ref_graph_i32_f64(ctypes.c_int(int(store_transposed)), _p(src), _p(dst), _p(w),
+                          ctypes.c_int32(num_vertices), ctypes.c_int64(ne), _p(offsets), _p(indices),
+                          _p(out_w) if w is not None else None)
+    return offsets, indices, (out_w if w is not None else None)
+
+
+def degree_ref(offsets, indices, num_vertices, major):
+    """degree_reference (cpp/tests/structure/degree_test.cpp:37-57)."""
+    lib = ref_lib()
+    offsets = np.ascontiguousarray(offsets, np.int64)
+    indices = np.ascontiguousarray(indices, np.int32)
+    out = np.zeros(num_vertices, np.int64)
+    lib.ref_degree_i32(_p(offsets), _p(indices), _p(out), ctypes.c_int32(num_vertices),
+                       ctypes.c_int(int(major)))
+    return out
+
+
+def weight_sum_ref(offsets, indices, weights, num_vertices, major):
+    """weight_sum_reference (cpp/tests/structure/weight_sum_test.cpp:37-59)."""
+    lib = ref_lib()
+    offsets = np.ascontiguousarray(offsets, np.int64)
+    indices = np.ascontiguousarray(indices, np.int32)
+    weights = np.ascontiguousarray(weights, np.float64)
+    out = np.zeros(num_vertices, np.float64)
+    lib.ref_weight_sum_i32_f64(_p(offsets), _p(indices), _p(weights), _p(out),
+                               ctypes.c_int32(num_vertices), ctypes.c_int(int(major)))
+    return out

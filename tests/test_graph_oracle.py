@@ -1,5 +1,6 @@
 """CPU: the numpy restatement of the integer graph-build path (oracle/graph_oracle.py)."""
 import numpy as np
+import pytest
 
 from oracle import graph_oracle as go
 from tests import util
@@ -85,3 +86,48 @@ def test_rmat_quadrant_ratios():
     # clip_and_flip keeps edges in the lower triangle (generate_rmat_test.cpp)
     s3, d3 = go.rmat_edgelist(scale, 1 << 14, seed=1, clip_and_flip=True)
     assert np.all(s3 >= d3)
+
+
+@pytest.mark.parametrize("case", ["karate", "rmat", "multi"])
+def test_compressed_build_degrees_and_weight_sums_match_the_compiled_reference(oracle_built, case):
+    """oracle/_ref holds the reference's own host references for the graph structure
+    (graph_test.cpp graph_reference, degree_test.cpp degree_reference, weight_sum_test.cpp
+    weight_sum_reference).  The oracle's renumber + compress must describe the same graph: per
+    row the same (neighbour, weight) pairs once the labels are mapped back - compared sorted, as
+    graph_test.cpp:154-190 does - and the same degrees / weight sums."""
+    if not oracle_built.ref_available():
+        pytest.skip("oracle/_ref not built")
+    rng = np.random.default_rng(12)
+    if case == "karate":
+        src, dst, w, nv, _ = util.load_mtx("karate.mtx", np.float64)
+    elif case == "rmat":
+        src, dst = util.rmat(10, seed=4)
+        nv = 1 << 10
+        w = rng.random(len(src))
+    else:  # parallel edges and self loops
+        nv = 50
+        src = rng.integers(0, nv, 4000).astype(np.int32)
+        dst = rng.integers(0, nv, 4000).astype(np.int32)
+        w = rng.integers(1, 9, 4000).astype(np.float64)
+    verts = np.arange(nv, dtype=np.int32)
+    r_off, r_idx, r_w = oracle_built.graph_ref(src, dst, w, nv, store_transposed=True)
+    labels, seg, nmaj, nmin = go.renumber_sg(dst.astype(np.int32), src.astype(np.int32), verts)
+    offs, idx, ww = go.compress_sorted(nmaj, nmin, w, 0, nv)
+    assert offs[-1] == r_off[-1] == len(src)
+    for r in range(nv):
+        ext = int(labels[r])
+        mine = sorted(zip(labels[idx[offs[r]:offs[r + 1]]].tolist(), ww[offs[r]:offs[r + 1]].tolist()))
+        ref = sorted(zip(r_idx[r_off[ext]:r_off[ext + 1]].tolist(),
+                         r_w[r_off[ext]:r_off[ext + 1]].tolist()))
+        assert mine == ref, f"row {ext}"
+    # degrees: rows are destinations, so major = in-degree, minor = out-degree
+    in_deg = oracle_built.degree_ref(r_off, r_idx, nv, True)
+    out_deg = oracle_built.degree_ref(r_off, r_idx, nv, False)
+    assert np.array_equal(np.diff(offs), in_deg[labels])
+    assert np.array_equal(go.out_weight_sums(idx, None, nv, np.int64), out_deg[labels])
+    # out-weight sums (the PageRank denominator): graph_view_t::compute_out_weight_sums
+    out_w = oracle_built.weight_sum_ref(r_off, r_idx, r_w, nv, False)
+    assert np.allclose(go.out_weight_sums(idx, ww, nv, np.float64), out_w[labels], rtol=1e-12)
+    in_w = oracle_built.weight_sum_ref(r_off, r_idx, r_w, nv, True)
+    mine_in = np.add.reduceat(np.append(ww, 0.0), offs[:-1]) * (np.diff(offs) > 0)
+    assert np.allclose(mine_in, in_w[labels], rtol=1e-12)
