@@ -64,3 +64,12 @@ _h54_auth = np.zeros(54)
 _h54_auth[[6, 8, 16, 29, 38, 45, 53]] = [0.321874, 0.123424, 0.595522, 0.0292397, 0.314164, 1,
                                          0.100368]
 H54_HITS = dict(epsilon=0.000001, max_iterations=100, hubs=_h54_hubs, authorities=_h54_auth)
+
+# cpp/tests/centrality/legacy/katz_centrality_test.cu:114-183 with datasets/ref/katz/*.csv: the ten
+# best vertices (best first) of Katz centrality on the UNWEIGHTED graph, alpha = 1 / (max out-degree
+# + 1), 100 iterations at most, tolerance 1e-6, normalised.  (netscience is commented out there.)
+KATZ_TOP10 = {
+    "karate.mtx": [33, 0, 32, 2, 1, 31, 3, 8, 13, 23],
+    "polbooks.mtx": [8, 12, 84, 3, 73, 72, 66, 30, 11, 47],
+    "dolphins.mtx": [14, 37, 45, 33, 51, 29, 20, 40, 50, 38],
+}

@@ -162,3 +162,17 @@ def test_hits_golden_vectors(oracle_built):
         hubs, auth, _, _ = co.hits(off, idx, dtype=dtype, max_iterations=p["max_iterations"],
                                    tolerance=p["epsilon"], normalize=False)
         assert gv.nearly_equal(hubs, p["hubs"]) and gv.nearly_equal(auth, p["authorities"])
+
+
+@pytest.mark.parametrize("name", sorted(gv.KATZ_TOP10))
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_katz_top10_golden_lists(oracle_built, name, dtype):
+    """The golden result files of the reference's legacy Katz test (datasets/ref/katz/*.csv,
+    legacy/katz_centrality_test.cu:114-183)."""
+    src, dst, _, nv, _ = util.load_mtx(name)
+    alpha = 1.0 / (np.bincount(src, minlength=nv).max() + 1)
+    for impl in ("port", "ref") if oracle_built.ref_available() else ("port",):
+        offsets, indices, _ = oracle_built.csc_from_coo(src, dst, None, nv)
+        kc, _ = oracle_built.katz(offsets, indices, None, dtype=dtype, alpha=alpha, beta=1.0,
+                                  epsilon=1e-6, max_iterations=100, normalize=True, impl=impl)
+        assert util.top_k(kc, 10).tolist() == gv.KATZ_TOP10[name]

@@ -242,3 +242,17 @@ def test_hits_file_client_runs():
     from tests.test_cpp_clients import _build
     r = subprocess.run([_build("hits_file_golden")], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "HITS_FILE_GOLDEN_OK" in r.stdout, (r.stdout, r.stderr)
+
+
+@pytest.mark.parametrize("name", sorted(gv.KATZ_TOP10))
+def test_katz_top10_golden_lists(cugraph, name):
+    """datasets/ref/katz/*.csv of the reference's legacy Katz test
+    (legacy/katz_centrality_test.cu:114-183) through the Python caller."""
+    src, dst, _, nv, _ = util.load_mtx(name)
+    G = cugraph.Graph(directed=True)
+    G.from_cudf_edgelist({"s": src.astype(np.int32), "d": dst.astype(np.int32)}, "s", "d",
+                         renumber=False, store_transposed=True)
+    alpha = 1.0 / (int(G.out_degree()["degree"].max()) + 1)
+    kc = _scores(cugraph.katz_centrality(G, alpha=alpha, beta=1.0, max_iter=100, tol=1e-6),
+                 "katz_centrality", nv)
+    assert util.top_k(kc, 10).tolist() == gv.KATZ_TOP10[name]
