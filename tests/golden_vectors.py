@@ -73,3 +73,28 @@ KATZ_TOP10 = {
     "polbooks.mtx": [8, 12, 84, 3, 73, 72, 66, 30, 11, 47],
     "dolphins.mtx": [14, 37, 45, 33, 51, 29, 20, 40, 50, 38],
 }
+
+# python/pylibcugraph/pylibcugraph/tests/test_pagerank.py:22-77: alpha 0.85, epsilon 1e-6, 500
+# iterations at most, float32, graphs made with renumber=False; compared with
+# pytest.approx(expected, 1e-4) (relative).  karate.csv / dolphins.csv hold the same directed edge
+# sets as the symmetric karate.mtx / dolphins.mtx expanded (unit weights).  "Simple_1" is P4 above;
+# "Simple_2" is the G6 graph.
+PLC_PAGERANK = dict(alpha=0.85, epsilon=1.0e-6, max_iterations=500, rel=1e-4)
+PLC_PAGERANK_RESULTS = {
+    "karate.mtx": np.array(
+        [0.096998, 0.052877, 0.057078, 0.035860, 0.021978, 0.029111, 0.029111, 0.024491, 0.029766,
+         0.014309, 0.021978, 0.009565, 0.014645, 0.029536, 0.014536, 0.014536, 0.016784, 0.014559,
+         0.014536, 0.019605, 0.014536, 0.014559, 0.014536, 0.031522, 0.021076, 0.021006, 0.015044,
+         0.025640, 0.019573, 0.026288, 0.024590, 0.037158, 0.071693, 0.100919]),
+    "dolphins.mtx": np.array(
+        [0.01696534, 0.02465084, 0.01333804, 0.00962903, 0.00507979, 0.01442816, 0.02005379,
+         0.01564308, 0.01709825, 0.02345867, 0.01510835, 0.00507979, 0.0048353, 0.02615709,
+         0.03214436, 0.01988301, 0.01662675, 0.03172837, 0.01939547, 0.01292825, 0.02464085,
+         0.01693892, 0.00541593, 0.00986347, 0.01690569, 0.01150429, 0.0112102, 0.01713019,
+         0.01484573, 0.02645844, 0.0153021, 0.00541593, 0.01330877, 0.02842296, 0.01591988,
+         0.00491821, 0.02061337, 0.02987523, 0.02393915, 0.00776477, 0.02196631, 0.01613769,
+         0.01761861, 0.02169104, 0.01283079, 0.02951408, 0.00882587, 0.01733948, 0.00526172,
+         0.00887672, 0.01923187, 0.03129924, 0.01207255, 0.00818102, 0.02165103, 0.00749415,
+         0.0083263, 0.0300956, 0.00496289, 0.01476788, 0.00619018, 0.01103916]),
+    "Simple_2": np.array([0.09902544, 0.17307726, 0.0732199, 0.1905103, 0.12379099, 0.34037617]),
+}

@@ -176,3 +176,20 @@ def test_katz_top10_golden_lists(oracle_built, name, dtype):
         kc, _ = oracle_built.katz(offsets, indices, None, dtype=dtype, alpha=alpha, beta=1.0,
                                   epsilon=1e-6, max_iterations=100, normalize=True, impl=impl)
         assert util.top_k(kc, 10).tolist() == gv.KATZ_TOP10[name]
+
+
+@pytest.mark.parametrize("name", sorted(gv.PLC_PAGERANK_RESULTS))
+def test_pylibcugraph_pagerank_golden_vectors(oracle_built, name):
+    """python/pylibcugraph/pylibcugraph/tests/test_pagerank.py:22-132."""
+    p = gv.PLC_PAGERANK
+    if name == "Simple_2":
+        src, dst, w, nv = gv.G6_SRC, gv.G6_DST, gv.G6_WGT, 6
+    else:
+        src, dst, w, nv, _ = util.load_mtx(name)
+    for impl in ("port", "ref") if oracle_built.ref_available() else ("port",):
+        offsets, indices, weights = oracle_built.csc_from_coo(src, dst, w, nv)
+        pr, _ = oracle_built.pagerank(offsets, indices, weights, dtype=np.float32, alpha=p["alpha"],
+                                      epsilon=p["epsilon"], max_iterations=p["max_iterations"],
+                                      impl=impl)
+        want = gv.PLC_PAGERANK_RESULTS[name]
+        assert np.all(np.abs(pr - want) <= p["rel"] * np.abs(want)), impl

@@ -256,3 +256,27 @@ def test_katz_top10_golden_lists(cugraph, name):
     kc = _scores(cugraph.katz_centrality(G, alpha=alpha, beta=1.0, max_iter=100, tol=1e-6),
                  "katz_centrality", nv)
     assert util.top_k(kc, 10).tolist() == gv.KATZ_TOP10[name]
+
+
+@pytest.mark.parametrize("name", sorted(gv.PLC_PAGERANK_RESULTS))
+def test_pylibcugraph_pagerank_golden_vectors(name):
+    """python/pylibcugraph/pylibcugraph/tests/test_pagerank.py:22-132 through the pylibcugraph
+    mirror: renumber=False, store_transposed=True, float32."""
+    from cugraph_forked_b200 import pylibcugraph as plc
+    p = gv.PLC_PAGERANK
+    if name == "Simple_2":
+        src, dst, w, nv = gv.G6_SRC, gv.G6_DST, gv.G6_WGT, 6
+    else:
+        src, dst, w, nv, _ = util.load_mtx(name)
+    t = lambda a, dt: torch.as_tensor(np.ascontiguousarray(a, dtype=dt)).cuda()
+    rh = plc.ResourceHandle()
+    g = plc.SGGraph(rh, plc.GraphProperties(is_symmetric=False, is_multigraph=False),
+                    t(src, np.int32), t(dst, np.int32), t(w, np.float32), store_transposed=True,
+                    renumber=False, do_expensive_check=False)
+    vertices, values = plc.pagerank(rh, g, None, None, None, None, p["alpha"], p["epsilon"],
+                                    p["max_iterations"], False)
+    assert vertices.dtype == torch.int32 and values.dtype == torch.float32
+    got = np.empty(nv)
+    got[vertices.cpu().numpy()] = values.cpu().numpy()
+    want = gv.PLC_PAGERANK_RESULTS[name]
+    assert np.all(np.abs(got - want) <= p["rel"] * np.abs(want))
