@@ -73,6 +73,17 @@ def pagerank(offsets, indices, weights=None, *, dtype=np.float32, alpha=0.85, ep
     if impl == "ref":
         fn = getattr(ref_lib(), "ref_pagerank_" + _sfx(dtype))
         fn.restype = ctypes.c_long
+        if fixed_iterations > 0:
+            # pagerank_reference has no iteration pin of its own: with epsilon = 0 its stop test
+            # (diff_sum < epsilon, pagerank_test.cpp:124) never holds, so it runs exactly
+            # max_iterations iterations, leaves their result in `pr`, and then trips its
+            # ASSERT_TRUE(iter < max_iterations), which the shim reports as -1.
+            rc = fn(_p(offsets), _p(indices), _p(weights), _p(pv), _p(pw), ctypes.c_int64(npers),
+                    _p(pr), ctypes.c_int64(nv), ctypes.c_double(alpha), ctypes.c_double(0.0),
+                    ctypes.c_long(fixed_iterations), ctypes.c_int(initial_guess is not None))
+            if rc != -1:
+                raise RuntimeError("pagerank_reference did not run to the pinned iteration count")
+            return pr, int(fixed_iterations)
         rc = fn(_p(offsets), _p(indices), _p(weights), _p(pv), _p(pw), ctypes.c_int64(npers), _p(pr),
                 ctypes.c_int64(nv), ctypes.c_double(alpha), ctypes.c_double(epsilon),
                 ctypes.c_long(max_iterations), ctypes.c_int(initial_guess is not None))

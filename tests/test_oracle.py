@@ -193,3 +193,17 @@ def test_pylibcugraph_pagerank_golden_vectors(oracle_built, name):
                                       impl=impl)
         want = gv.PLC_PAGERANK_RESULTS[name]
         assert np.all(np.abs(pr - want) <= p["rel"] * np.abs(want)), impl
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_reference_pinned_iterations_equals_port(dtype):
+    """cpu_oracle.pagerank(impl="ref", fixed_iterations=k): the reference's pagerank_reference run
+    with epsilon 0 and max_iterations k does exactly k iterations; bit-identical to the port."""
+    if not cpu_oracle.ref_available():
+        pytest.skip("oracle/_ref not built")
+    src, dst = util.rmat(12, seed=5)
+    o, i, _ = cpu_oracle.csc_from_coo(src, dst, None, 1 << 12)
+    for k in (1, 7):
+        a, _ = cpu_oracle.pagerank(o, i, None, dtype=dtype, impl="ref", fixed_iterations=k)
+        b, _ = cpu_oracle.pagerank(o, i, None, dtype=dtype, impl="port", fixed_iterations=k)
+        assert np.array_equal(a, b)

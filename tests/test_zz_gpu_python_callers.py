@@ -12,13 +12,9 @@ import torch
 from tests import golden_vectors as gv
 from tests import util
 
-# Written after round 1's GPU budget was spent: every case here has run against the oracle-backed
-# stand-in on the CPU (tests/test_python_callers*.py and a dry run of this very file), none on
-# hardware yet.  Until the first hardware run they report as XPASS / XFAIL instead of deciding the
-# suite; scripts/gpu_r2_first.sh is that run, after which the marker goes.
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.xfail(strict=False, reason="first hardware run pending (CPU stand-in "
-                                                     "run is green)")]
+# First hardware run: round 2, call r2a (profiles/r2_notes.md) - all cases passed; the
+# non-strict xfail marker of round 1 is gone, a regression now fails the suite.
+pytestmark = pytest.mark.gpu
 
 
 @pytest.fixture(scope="module")

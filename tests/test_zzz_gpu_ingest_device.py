@@ -9,13 +9,9 @@ import numpy as np
 import pytest
 import torch
 
-# Opt-in, like the parser itself (io.read_*(parser="device")): the kernels were written after
-# round 1's GPU budget was spent and have only run in host emulation.  scripts/gpu_r2_first.sh
-# sets the variable; once they have passed on hardware the guard goes away.
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("B200_TEST_DEVICE_INGEST", "0") != "1",
-                                 reason="device text parser is opt-in until its first hardware run "
-                                        "(set B200_TEST_DEVICE_INGEST=1)")]
+# First hardware run: round 2, call r2a (profiles/r2_notes.md) - 11 cases passed; the opt-in
+# guard of round 1 is gone.
+pytestmark = pytest.mark.gpu
 
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
 
