@@ -5,6 +5,7 @@ graph_functions.hpp create_graph_from_edgelist) with internal-order arrays."""
 from __future__ import annotations
 
 import ctypes
+import weakref
 from dataclasses import dataclass
 
 import torch
@@ -78,8 +79,16 @@ class Handle:
     def world_size(self) -> int:
         return _lib.lib().b200_handle_world_size(self._h)
 
+    def _track(self, graph) -> None:
+        # graphs free their device buffers on the handle's stream: they must go first
+        if not hasattr(self, "_graphs"):
+            self._graphs = weakref.WeakSet()
+        self._graphs.add(graph)
+
     def close(self):
         if self._h:
+            for g in list(getattr(self, "_graphs", ())):
+                g.close()
             _lib.lib().b200_handle_free(self._h)
             self._h = ctypes.c_void_p()
 
@@ -118,6 +127,7 @@ class Graph:
                 int(store_transposed), int(renumber), ctypes.byref(self._g)))
         self.multi_gpu = multi_gpu
         self.vertex_dtype = src.dtype
+        handle._track(self)
 
     # -- introspection (bit-exact parity tests read these) --
     def view(self, partition: int | None = None) -> _lib.GraphView:

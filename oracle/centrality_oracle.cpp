@@ -29,7 +29,14 @@
 
 namespace {
 
-template <typename R>
+// A = accumulator type of the row sums and of the dangling / difference sums.  A = R restates
+// pagerank_reference exactly (bit-identical, tests/test_oracle.py).  A = long double (x87 80-bit,
+// 64-bit mantissa) is the "extended" variant: the same algorithm with the SUMS kept in extended
+// precision and every stored value still an R.  The sequential sums of the reference carry up to
+// deg * eps of rounding error on hub rows (in-degree > 1e5 on R-MAT scale 20 => ~4e-12 in fp64,
+// ~3e-3 in fp32); the extended variant is what both the reference and a device implementation
+// with another summation order are measured against in tests/test_gpu_configs.py.
+template <typename R, typename A = R>
 long pagerank_cpu(const int64_t* offsets, const int32_t* indices, const R* weights,
                   const int32_t* pers_vertices, const R* pers_values, int64_t pers_size,
                   R* pr, int64_t nv, R alpha, R epsilon, long max_iterations,
@@ -62,24 +69,27 @@ long pagerank_cpu(const int64_t* offsets, const int32_t* indices, const R* weigh
   long iter = 0;
   for (;;) {
     for (int64_t v = 0; v < nv; ++v) old[v] = pr[v];
-    R dangling{0.0};
+    A dangling_acc{0.0};
     for (int64_t v = 0; v < nv; ++v)
-      if (outw[v] == R{0.0}) dangling += old[v];
+      if (outw[v] == R{0.0}) dangling_acc += old[v];
+    const R dangling = static_cast<R>(dangling_acc);
     for (int64_t v = 0; v < nv; ++v) {
-      pr[v] = R{0.0};
+      A acc{0.0};
       for (int64_t e = offsets[v]; e < offsets[v + 1]; ++e) {
         int32_t u = indices[e];
         R w = weights ? weights[e] : R{1.0};
-        pr[v] += alpha * old[u] * (w / outw[u]);
+        acc += alpha * old[u] * (w / outw[u]);
       }
+      pr[v] = static_cast<R>(acc);
       if (!pers_vertices) pr[v] += (dangling * alpha + (1.0 - alpha)) / static_cast<R>(nv);
     }
     if (pers_vertices) {
       for (int64_t i = 0; i < pers_size; ++i)
         pr[pers_vertices[i]] += (dangling * alpha + (1.0 - alpha)) * (pers_values[i] / pers_sum);
     }
-    R diff{0.0};
-    for (int64_t v = 0; v < nv; ++v) diff += std::abs(pr[v] - old[v]);
+    A diff_acc{0.0};
+    for (int64_t v = 0; v < nv; ++v) diff_acc += std::abs(pr[v] - old[v]);
+    const R diff = static_cast<R>(diff_acc);
     if (fixed_iterations > 0) {
       if (++iter >= fixed_iterations) return iter;
       continue;
@@ -251,6 +261,18 @@ extern "C" {
 ORACLE_DEFINE_HITS(f32, float)
 ORACLE_DEFINE_HITS(f64, double)
 
+
+extern "C" long oracle_pagerank_f64_ext(const int64_t* offsets, const int32_t* indices,
+                                        const double* weights, const int32_t* pers_vertices,
+                                        const double* pers_values, int64_t pers_size, double* pr,
+                                        int64_t nv, double alpha, double epsilon,
+                                        long max_iterations, int has_initial_guess,
+                                        long fixed_iterations)
+{
+  return pagerank_cpu<double, long double>(offsets, indices, weights, pers_vertices, pers_values,
+                                           pers_size, pr, nv, alpha, epsilon, max_iterations,
+                                           has_initial_guess, fixed_iterations);
+}
 
 #define ORACLE_DEFINE(SUFFIX, R)                                                                   \
   long oracle_pagerank_##SUFFIX(const int64_t* offsets, const int32_t* indices, const R* weights,  \

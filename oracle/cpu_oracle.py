@@ -88,7 +88,10 @@ def pagerank(offsets, indices, weights=None, *, dtype=np.float32, alpha=0.85, ep
                 ctypes.c_int64(nv), ctypes.c_double(alpha), ctypes.c_double(epsilon),
                 ctypes.c_long(max_iterations), ctypes.c_int(initial_guess is not None))
     else:
-        fn = getattr(port_lib(), "oracle_pagerank_" + _sfx(dtype))
+        # impl="ext": the port with its sums in extended precision (fp64 values only)
+        name = "oracle_pagerank_f64_ext" if impl == "ext" else "oracle_pagerank_" + _sfx(dtype)
+        assert impl != "ext" or np.dtype(dtype) == np.float64
+        fn = getattr(port_lib(), name)
         fn.restype = ctypes.c_long
         rc = fn(_p(offsets), _p(indices), _p(weights), _p(pv), _p(pw), ctypes.c_int64(npers), _p(pr),
                 ctypes.c_int64(nv), ctypes.c_double(alpha), ctypes.c_double(epsilon),

@@ -64,27 +64,52 @@ def test_pagerank_rmat_s20_vs_reference(handle, dtype):
     assert st.converged and st.gpu_launches >= st.iterations
     ext = util.to_external(pr.cpu().numpy(), labels, nv)
     assert abs(float(ext.astype(np.float64).sum()) - 1.0) < (1e-4 if dtype == np.float32 else 1e-9)
-    # (1) the fp64 port at the GPU's iteration count: the tolerance north_star states
+    # (1) the tolerance north_star states, at the GPU's iteration count.  fp32: against the fp64
+    #     port.  fp64: against the port with its sums in extended precision - the reference's
+    #     sequential fp64 row sums carry up to in-degree * 2^-53 of rounding error themselves
+    #     (4e-12 on this graph's hub rows, measured on B200 in call r2b), so the plain port is
+    #     held to that bound and the extended one to 1e-12; all three differences are printed.
     ref64, _ = cpu_oracle.pagerank(offsets, indices, None, dtype=np.float64, alpha=0.85,
                                    fixed_iterations=st.iterations)
     err = util.rel_err(ext, ref64)
-    assert err.max() <= TOL[dtype], f"max rel err vs fp64 oracle {err.max():.3e}"
+    if dtype == np.float64:
+        refx, _ = cpu_oracle.pagerank(offsets, indices, None, dtype=np.float64, alpha=0.85,
+                                      fixed_iterations=st.iterations, impl="ext")
+        errx = util.rel_err(ext, refx)
+        max_deg = int(np.diff(offsets).max())
+        print(f"\n[s20 f64] max rel err: GPU vs extended-sum oracle {errx.max():.3e}, GPU vs "
+              f"pagerank_reference port {err.max():.3e}, port vs extended {util.rel_err(ref64, refx).max():.3e}"
+              f" (max in-degree {max_deg})")
+        assert errx.max() <= 1e-12, f"max rel err vs extended-sum oracle {errx.max():.3e}"
+        assert err.max() <= 1e-12 + max_deg * 2.0**-53
+        assert _same_top(ext, refx)
+    else:
+        assert err.max() <= TOL[dtype], f"max rel err vs fp64 oracle {err.max():.3e}"
     assert _same_top(ext, ref64)
-    # (2) the reference's own compiled pagerank_reference, same precision, to convergence
+    # (2) the reference's own compiled pagerank_reference in fp64, to convergence, at the
+    #     reference's own bound (pagerank_test.cpp:355-362)
     impl = "ref" if cpu_oracle.ref_available() else "port"
-    ref, _ = cpu_oracle.pagerank(offsets, indices, None, dtype=dtype, alpha=0.85, epsilon=1e-6,
-                                 max_iterations=500, impl=impl)
-    thr = np.maximum(np.maximum(ext, ref) * 1e-3, 1e-3 / nv)   # pagerank_test.cpp:355-362
+    ref, _ = cpu_oracle.pagerank(offsets, indices, None, dtype=np.float64, alpha=0.85,
+                                 epsilon=1e-6, max_iterations=500, impl=impl)
+    thr = np.maximum(np.maximum(ext, ref) * 1e-3, 1e-3 / nv)
     assert np.all(np.abs(ext - ref) < thr)
     if dtype == np.float64:
         # fp64: the reference itself is inside the tolerance, and stops at the same iteration
         _, it_port = cpu_oracle.pagerank(offsets, indices, None, dtype=np.float64, alpha=0.85,
                                          epsilon=1e-6, max_iterations=500)
         assert it_port == st.iterations
-        assert util.rel_err(ext, ref).max() <= 1e-12
+        assert util.rel_err(ext, ref).max() <= 1e-12 + max_deg * 2.0**-53
         assert _same_top(ext, ref)
     else:
-        _report("s20 f32", ext, ref)
+        # fp32 pagerank_reference sums every row sequentially in fp32: on the hub rows of this
+        # graph (in-degree > 1e5) it is itself ~3e-3 away from its own fp64 result (measured on
+        # B200, call r2b: 3.1571e-3 vs 3.1472e-3 for the top vertex), i.e. outside the reference's
+        # own 1e-3 bound.  Reported, not asserted.
+        ref32, _ = cpu_oracle.pagerank(offsets, indices, None, dtype=np.float32, alpha=0.85,
+                                       epsilon=1e-6, max_iterations=500, impl=impl)
+        _report("s20 f32", ext, ref32)
+        e32 = util.rel_err(ref32, ref)
+        print(f"[s20 f32] fp32 pagerank_reference vs its own fp64 run: max rel err {e32.max():.3e}")
 
 
 def test_pagerank_rmat_s24_f32_vs_reference(handle):
@@ -107,6 +132,4 @@ def test_pagerank_rmat_s24_f32_vs_reference(handle):
     assert _same_top(ext, ref64)
     ref32, _ = cpu_oracle.pagerank(offsets, indices, None, dtype=np.float32, alpha=0.85,
                                    fixed_iterations=iters, impl=impl)
-    thr = np.maximum(np.maximum(ext, ref32) * 1e-3, 1e-3 / nv)
-    assert np.all(np.abs(ext - ref32) < thr)
-    _report("s24 f32, 5 iterations", ext, ref32)
+    _report("s24 f32, 5 iterations", ext, ref32)    # reported only: see the s20 case
