@@ -154,6 +154,7 @@ SIGNATURES = {
     "b200_graph_out_weight_sums": (_i, [_vp, _vp, _i, _vp]),
     "b200_graph_in_degrees": (_i, [_vp, _vp, _vp]),
     "b200_spmv_pull": (_i, [_vp, _vp, _i, _vp, _d, _d, _vp]),
+    "b200_spmv_pull_noalloc": (_i, [_vp, _vp, _i, _vp, _d, _d, _vp]),
     "b200_pagerank": (_i, [_vp, _vp, ctypes.POINTER(PagerankParams), _vp,
                            ctypes.POINTER(CentralityStats)]),
     "b200_katz_centrality": (_i, [_vp, _vp, ctypes.POINTER(KatzParams), _vp,

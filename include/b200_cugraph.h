@@ -127,6 +127,20 @@ int b200_graph_in_degrees(b200_handle_t* h, const b200_graph_t* g, void* out);
 int b200_spmv_pull(b200_handle_t* h, const b200_graph_t* g, int value_type, const void* x,
                    double scale, double init, void* y);
 
+/* The same operation for callers that may not allocate (CUDA-graph capture, serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Calls no cudaMalloc / cudaFree / allocating library routine and does not
+ * synchronise: two kernels are enqueued on the handle's stream and the call returns.  Its scratch
+ * (two partial sums per window of 4096 CSC positions) lives in a static __device__ array of
+ * 4 MiB that every GPU loading the library holds until exit; graphs with more than 2^30 edges are
+ * rejected with B200 error "invalid input" and a message naming the limit.  All calls share that
+ * array: calls that overlap on one GPU (two streams, threads or handles) race - serialise them.
+ * Single-GPU graphs; value_type B200_FLOAT32 / B200_FLOAT64; weights are read in their stored
+ * type.  Same result as b200_spmv_pull up to floating-point association (sums are kept in fp64
+ * and combined in a fixed order, so repeated calls are bit-identical). */
+int b200_spmv_pull_noalloc(b200_handle_t* h, const b200_graph_t* g, int value_type, const void* x,
+                           double scale, double init, void* y);
+
 /* -------------------------------------------------------------------------------------------
  * drivers
  * ------------------------------------------------------------------------------------------- */
