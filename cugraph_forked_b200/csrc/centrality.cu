@@ -11,6 +11,7 @@
 #include <climits>
 
 #include "banded.cuh"
+#include "sell.cuh"
 #include "centrality.cuh"
 #include "spmv.cuh"
 
@@ -169,6 +170,9 @@ struct pull_launcher {
   int band_kernel{2};            // phase-1 formulation: 2 = scratch-column kernel, 1 = first one
   dbuf<int32_t> band_queue;      // two unit counters of phase 1, used alternately
   int64_t band_launches{0};
+  // round-2 layout (sell.cuh): both phases as sliced-ELL kernels; replaces `banded` when enabled
+  sell_layout* sell{nullptr};
+  int sell_ctas1{0};             // phase-1 grid (one CTA per SM)
 
   void init(b200_handle* h_, b200_graph* g, edge_partition* ep_);
 
@@ -249,7 +253,27 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
   // multi-GPU: every edge partition gets its own layout (bands of its minor range); the
   // opt-in fused rectangle keeps the single-phase kernel
   const bool is_fused = !g->fused.empty() && ep == &g->fused[0];
-  if (tiled && !is_fused && !ep->offsets64 && env_int("B200_BANDED", kBandedDefault) != 0) {
+  sell = nullptr;
+  if (tiled && !is_fused && !ep->offsets64 && env_int("B200_BANDED", kBandedDefault) != 0 &&
+      env_int("B200_LAYOUT", 2) == 2) {
+    sell_layout* sl = sell_get<RT>(h, *ep, weights);
+    if (sl && sl->enabled) {
+      sell = sl;
+      pval.alloc(static_cast<size_t>(sl->num_partials) + 1, s, 8);
+      // the entry behind the last partial is the zero the padding slots of phase 2 read
+      CUDA_TRY(cudaMemsetAsync(pval.data() + sl->num_partials, 0, sizeof(RT), s));
+      band_queue.alloc(4, s);   // [0,1] phase 1, [2,3] phase 2: used alternately
+      CUDA_TRY(cudaMemsetAsync(band_queue.data(), 0, 16, s));
+      band_launches = 0;
+      CUDA_TRY(cudaFuncSetAttribute(sell_band_kernel<RT, true>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    static_cast<int>(sell_geom<RT>::smem)));
+      CUDA_TRY(cudaFuncSetAttribute(sell_band_kernel<RT, false>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    static_cast<int>(sell_geom<RT>::smem)));
+    }
+  }
+  if (!sell && tiled && !is_fused && !ep->offsets64 && env_int("B200_BANDED", kBandedDefault) != 0) {
     const int T0 = T, rowcap0 = rowcap;
     if (cfg_id == 0 && env_int("B200_BANDED_CFG", 1) != 0) {
       banded_tiles = true;
@@ -293,6 +317,21 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
       T            = T0;
       rowcap       = rowcap0;
     }
+  }
+  if (sell) {
+    sell_ctas1 = h->sm_count;
+    int per_sm = std::max(1, env_int("B200_SELL_CTAS_PER_SM", 8));
+    if (g->multi_gpu && h->size > 1) {
+      sell_ctas1 = std::max(1, sell_ctas1 - std::max(0, env_int("B200_MG_RESERVED_SMS", 16)));
+    }
+    main_ctas = sell_ctas1 * per_sm;   // phase-2 grid: 256-thread CTAs, tasks claimed dynamically
+    int64_t want_tail = div_up(std::max<int64_t>(sell->num_long_rows, 1), 32);
+    tail_ctas         = static_cast<int>(std::min<int64_t>(want_tail, 8 * h->sm_count));
+    slots = main_ctas + tail_ctas;
+    chunk_partials.alloc(static_cast<size_t>(std::max<int64_t>(sell->num_chunks, 1)), s);
+    cta_partials.alloc(static_cast<size_t>(2 * slots), s);
+    CUDA_TRY(cudaMemsetAsync(cta_partials.data(), 0, sizeof(double) * 2 * slots, s));
+    return;
   }
   if (tiled) {
     if (!banded) build_schedule(h, *ep, T, rowcap);
@@ -339,6 +378,51 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
     } else {
       if (weighted) go(int32_t{}, std::true_type{}); else go(int32_t{}, std::false_type{});
     }
+    CUDA_TRY(cudaGetLastError());
+    ++launches;
+    return;
+  }
+  if (sell) {
+    sell_params1<RT> A{};
+    A.x          = x;
+    A.pval       = pval.data();
+    A.idx        = sell->p1_idx.data();
+    A.w          = weighted ? reinterpret_cast<const RT*>(sell->p1_w.data()) : nullptr;
+    A.sbase      = sell->p1_sbase.data();
+    A.slot       = sell->p1_slot.data();
+    A.tasks      = sell->p1_tasks.data();
+    A.units      = sell->p1_units.data();
+    A.num_units  = static_cast<int32_t>(sell->p1_num_units);
+    A.queue      = band_queue.data() + (band_launches & 1);
+    A.queue_next = band_queue.data() + ((band_launches + 1) & 1);
+    A.num_minors = ep->num_minors;
+    A.state      = state;
+    const size_t smem = sell_geom<RT>::smem;
+    if (weighted) sell_band_kernel<RT, true><<<sell_ctas1, kBandThreads, smem, s>>>(A);
+    else          sell_band_kernel<RT, false><<<sell_ctas1, kBandThreads, smem, s>>>(A);
+    CUDA_TRY(cudaGetLastError());
+    ++launches;
+    sell_params2<RT> Q{};
+    Q.x              = x;
+    Q.pval           = pval.data();
+    Q.x_split        = sell->x_split;
+    Q.idx            = sell->p2_idx.data();
+    Q.w              = weighted ? reinterpret_cast<const RT*>(sell->p2_w.data()) : nullptr;
+    Q.sbase          = sell->p2_sbase.data();
+    Q.row            = sell->p2_row.data();
+    Q.chunk_slices   = sell->p2_chunk_slices;
+    Q.num_chunks     = sell->num_chunks;
+    Q.task_first     = sell->p2_task_first.data();
+    Q.num_tasks      = static_cast<int32_t>(sell->p2_num_tasks);
+    Q.queue          = band_queue.data() + 2 + (band_launches & 1);
+    Q.queue_next     = band_queue.data() + 2 + ((band_launches + 1) & 1);
+    Q.chunk_partials = chunk_partials.data();
+    Q.cta_partials   = parts;
+    Q.slots          = slots;
+    Q.state          = state;
+    ++band_launches;
+    if (weighted) sell_rows_kernel<RT, true, EPI><<<main_ctas, kSell2Threads, 0, s>>>(Q, epi);
+    else          sell_rows_kernel<RT, false, EPI><<<main_ctas, kSell2Threads, 0, s>>>(Q, epi);
     CUDA_TRY(cudaGetLastError());
     ++launches;
     return;
@@ -473,6 +557,11 @@ void pull_launcher<RT>::tail(EPI const& epi, iter_state* state, double epsilon, 
   P.long_row_chunk_first = tiled ? kp->long_row_chunk_first.data() : nullptr;
   P.chunk_partials       = chunk_partials.data();
   P.num_long_rows        = tiled ? kp->num_long_rows : 0;
+  if (sell) {
+    P.long_row_ids         = sell->long_row_ids.data();
+    P.long_row_chunk_first = sell->long_row_chunk_first.data();
+    P.num_long_rows        = sell->num_long_rows;
+  }
   P.cta_partials         = finalize ? cta_partials.data() : nullptr;
   P.slots                = slots;
   P.main_ctas            = main_ctas;

@@ -168,6 +168,7 @@ struct b200_handle {
 namespace b200 {
 
 struct banded_layout;  // banded.cuh: the pre-reduction layout derived from a CSC rectangle
+struct sell_layout;    // sell.cuh: the round-2 layout (lane owns a segment)
 
 // One CSC (or CSR) rectangle + its kernel schedule.
 struct edge_partition {
@@ -202,6 +203,7 @@ struct edge_partition {
   // banded pre-reduction layouts derived from this rectangle, one per result width
   // ([0] 4-byte, [1] 8-byte values), built on first use by the pull launcher (banded.cu)
   std::shared_ptr<banded_layout> banded[2];
+  std::shared_ptr<sell_layout> sell[2];
 };
 
 }  // namespace b200
