@@ -34,7 +34,11 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--scale", type=int, default=24)
     ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
-    ap.add_argument("--cpu-scale", type=int, default=20, help="scale of the bounded CPU sample")
+    ap.add_argument("--cpu-scale", type=int, default=None,
+                    help="scale of the CPU sample (default: the same graph as the GPU arm)")
+    ap.add_argument("--cpu-iterations", type=int, default=3,
+                    help="pinned iterations of the cpu_baseline sample of the b200 arm")
+    ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     return ap.parse_args()
@@ -108,59 +112,123 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------
-# CPU arm: the reference's own host pagerank_reference (oracle/_ref) on a bounded sample
+# CPU arm: the reference's own host pagerank_reference (oracle/_ref) on the SAME graph
 # ------------------------------------------------------------------------------------------
-def cpu_reference_gteps(scale, dtype):
-    """Times oracle/_ref (the reference's pagerank_reference compiled from /root/reference), or
-    the bit-identical port when _ref was not built, on RMAT `scale` to convergence.  Single
-    thread: the reference's host implementation is scalar code."""
+def workload_string(scale, dtype):
+    nv, ne = 1 << scale, EDGE_FACTOR << scale
+    return (f"PageRank {dtype} on RMAT scale {scale} ef {EDGE_FACTOR} ({nv} V, {ne} E), "
+            f"a/b/c={A}/{B}/{C}, alpha={ALPHA}; a step = one power iteration (one pull-kernel pass "
+            "over the graph)")
+
+
+def cpu_reference_gteps(scale, dtype, iterations, edges=None):
+    """Times oracle/_ref (the reference's pagerank_reference compiled from /root/reference; the
+    bit-identical port when _ref was not built) for `iterations` pinned power iterations on the
+    R-MAT graph of `scale` - the same edge list the GPU arm runs (the generators are
+    bit-identical twins).  One thread: the reference's host implementation is scalar code.  The
+    call includes pagerank_reference's own out-weight pass over the edges."""
     import numpy as np
-    from oracle import cpu_oracle, graph_oracle
+    from oracle import cpu_oracle
     cpu_oracle.build()
-    ne = EDGE_FACTOR << scale
-    nv = 1 << scale
-    src, dst = graph_oracle.rmat_edgelist(scale, ne, a=A, b=B, c=C, seed=0)
-    offsets, indices, _ = cpu_oracle.csc_from_coo(src, dst, None, nv)
+    ne, nv = EDGE_FACTOR << scale, 1 << scale
+    t0 = time.perf_counter()
+    src, dst = edges if edges is not None else cpu_oracle.rmat_edgelist_fast(scale, ne, a=A, b=B, c=C, seed=0)
+    offsets, indices = cpu_oracle.csc_from_coo_fast(src, dst, nv, threads=8)
+    del src, dst
+    prep = time.perf_counter() - t0
     npdt = np.float32 if dtype == "f32" else np.float64
     kind = "reference" if cpu_oracle.ref_available() else "port"
     t0 = time.perf_counter()
-    _, it = cpu_oracle.pagerank(offsets, indices, None, dtype=npdt, alpha=ALPHA, epsilon=EPSILON,
-                                max_iterations=10000, impl="ref" if kind == "reference" else "port")
+    cpu_oracle.pagerank(offsets, indices, None, dtype=npdt, alpha=ALPHA, fixed_iterations=iterations,
+                        impl="ref" if kind == "reference" else "port")
     dt = time.perf_counter() - t0
-    if kind == "reference":
-        # the shim cannot see the iteration count; the port is bit-identical (tests/test_oracle.py)
-        _, it = cpu_oracle.pagerank(offsets, indices, None, dtype=npdt, alpha=ALPHA,
-                                    epsilon=EPSILON, max_iterations=10000, impl="port")
-    return {"value": ne * it / dt / 1e9, "unit": "GTEPS", "cores": 1, "kind": kind,
-            "sample": f"RMAT scale {scale} ef {EDGE_FACTOR} ({ne} edges), {dtype}, {it} iterations "
-                      f"to epsilon {EPSILON:g} in {dt:.2f} s on 1 of {os.cpu_count()} host cores"}
+    return {"value": ne * iterations / dt / 1e9, "unit": "GTEPS", "cores": 1, "kind": kind,
+            "scale": scale, "iterations": iterations, "seconds": dt,
+            "sample": f"RMAT scale {scale} ef {EDGE_FACTOR} ({ne} edges, the GPU arm's graph), "
+                      f"{dtype}, {iterations} pinned iterations in {dt:.2f} s on 1 of "
+                      f"{os.cpu_count()} host cores (input built in {prep:.1f} s, untimed)"}
+
+
+def bounded_iterations(scale, want, budget_s=120.0, assumed_gteps=0.2):
+    """iterations of the scalar CPU code that fit the time budget (it runs ~0.2-0.35 GTEPS)"""
+    ne = EDGE_FACTOR << scale
+    return max(1, min(want, int(budget_s * assumed_gteps * 1e9 / ne)))
 
 
 def run_reference(args, rank, world):
     if rank != 0:
         return
-    scale = min(args.cpu_scale, args.scale)
-    vals = []
-    for _ in range(max(1, min(args.steps, 1))):  # one bounded sample per run (tens of seconds)
-        vals.append(cpu_reference_gteps(scale, args.dtype))
-    best = max(vals, key=lambda v: v["value"])
-    nv, ne = 1 << args.scale, EDGE_FACTOR << args.scale
+    scale = args.scale if args.cpu_scale is None else args.cpu_scale
+    iters = bounded_iterations(scale, max(args.steps, 1))
+    best = cpu_reference_gteps(scale, args.dtype, iters)
     line = {
         "impl": "reference", "metric": "pagerank_gteps", "value": best["value"], "unit": "GTEPS",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": None, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": args.dtype, "data": "synthetic",
-        "config": {"workload": f"PageRank {args.dtype} on RMAT scale {args.scale} ef {EDGE_FACTOR} "
-                               f"({nv} V, {ne} E), a/b/c={A}/{B}/{C}, alpha={ALPHA}",
+        "ms_per_step": best["seconds"] / iters * 1e3, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+        "config": {"workload": workload_string(scale, args.dtype),
+                   "same_config": scale == args.scale,
                    "reference_arm": "the reference's host pagerank_reference "
-                                    "(cpp/tests/link_analysis/pagerank_test.cpp:42-130) on CPU; "
-                                    "bounded sample, see cpu_baseline.sample"},
+                                    "(cpp/tests/link_analysis/pagerank_test.cpp:42-130) on CPU, "
+                                    f"{iters} pinned iterations; see cpu_baseline.sample"},
         "cpu_baseline": best,
         "e2e": {"value": best["value"], "unit": "GTEPS", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def parity_check(engine, h, rank, world, dtype, tdt):
+    """Self-check of the path this process group is about to time (SCALE carried no
+    correctness evidence): R-MAT scale 20 through the same N-rank graph build + PageRank, 20
+    pinned iterations, gathered to rank 0 and compared per vertex with the CPU oracle (fp64 port,
+    pinned bit-identical to the compiled reference; extended-precision sums for f64)."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    scale, iters = 20, 20
+    nv, ne = 1 << scale, EDGE_FACTOR << scale
+    per = ne // world
+    first = rank * per
+    cnt = per if rank < world - 1 else ne - first
+    src, dst = engine.generate_rmat_edgelist(h, scale, cnt, a=A, b=B, c=C, seed=0, first_edge=first)
+    vper = nv // world
+    verts = torch.arange(rank * vper, nv if rank == world - 1 else (rank + 1) * vper,
+                         dtype=torch.int32, device="cuda")
+    g = engine.Graph(h, src, dst, vertices=verts, multi_gpu=world > 1)
+    pr, st = engine.pagerank(g, alpha=ALPHA, epsilon=EPSILON, dtype=tdt, fixed_iterations=iters)
+    ids = g.renumber_map().cpu().numpy()
+    vals = pr.cpu().numpy()
+    del g, src, dst
+    if world > 1:
+        parts = [None] * world if rank == 0 else None
+        dist.gather_object((ids, vals), parts, dst=0)
+    else:
+        parts = [(ids, vals)]
+    if rank != 0:
+        return None
+    from oracle import cpu_oracle
+    cpu_oracle.build()
+    ext = np.full(nv, np.nan, dtype=np.float64)
+    for i, v in parts:
+        ext[i] = v
+    es, ed = cpu_oracle.rmat_edgelist_fast(scale, ne, a=A, b=B, c=C, seed=0)
+    offsets, indices = cpu_oracle.csc_from_coo_fast(es, ed, nv, threads=8)
+    ref, _ = cpu_oracle.pagerank(offsets, indices, None, dtype=np.float64, alpha=ALPHA,
+                                 fixed_iterations=iters, impl="ext" if dtype == "f64" else "port")
+    err = np.abs(ext - ref) / np.maximum(np.abs(ref), np.finfo(np.float64).tiny)
+    tol = 1e-5 if dtype == "f32" else 1e-12
+    top = lambda x: np.lexsort((np.arange(nv), -x))[:100]
+    complete = bool(not np.isnan(ext).any())
+    max_err = float(np.nanmax(err)) if complete else float("inf")
+    total = float(np.nansum(ext))
+    same_top = bool(np.array_equal(top(ext), top(ref)))
+    ok = complete and max_err <= tol and abs(total - 1.0) < (1e-4 if dtype == "f32" else 1e-9) and same_top
+    return {"workload": f"PageRank {dtype}, RMAT scale {scale}, {iters} pinned iterations, {world} rank(s)",
+            "oracle": "fp64 port of pagerank_reference" + (" with extended-precision sums" if dtype == "f64" else ""),
+            "max_rel_err": max_err, "tolerance": tol, "sum": total, "top100_identical": same_top,
+            "pass": bool(ok)}
 
 
 def run_b200(args, rank, world):
@@ -191,6 +259,12 @@ def run_b200(args, rank, world):
         h = engine.Handle.multi_gpu(uid[0], rank, world, rows)
     else:
         h = engine.Handle()
+
+    # ---- self-check of this N-rank path against the CPU oracle, before anything is timed ----
+    parity = None
+    if not args.no_parity:
+        parity = parity_check(engine, h, rank, world, args.dtype, tdt)
+        torch.cuda.empty_cache()
 
     # ---- synthetic input: this rank's slice of the R-MAT edge stream, resident in HBM ----
     per = ne // world
@@ -228,19 +302,27 @@ def run_b200(args, rank, world):
         b_iter = cols * (nv // world + 1) * 4 + (ne // world) * (4 + val_size)
     else:
         b_iter = algorithmic_bytes(nv, ne, val_size)
-    # the single-GPU SpMV is two launches when the banded pre-reduction is on (band_reduce_kernel
-    # + pull_tiles_kernel, timed together as one SpMV) and one otherwise; + the tail kernel
-    banded = os.environ.get("B200_BANDED", "1") != "0" and (
-        world > 1 or st.gpu_launches >= 3 * max(st.iterations, 1))
+    # one SpMV = phase 1 (pre-reduction of the cells of x's bands from shared memory) + phase 2
+    # (rows of the reduced CSC), timed together by the library; + the small tail kernel
+    if os.environ.get("B200_BANDED", "1") == "0":
+        path, kernels = "tiled", "pull_tiles_kernel"
+    elif os.environ.get("B200_LAYOUT", "2") != "2":
+        path, kernels = "banded-r1", "band_reduce_kernel + pull_tiles_kernel (one SpMV)"
+    else:
+        path, kernels = "sell-r2", "sell_band_kernel + sell_rows_kernel (one SpMV)"
     kern_ms = st.spmv_ms / max(st.spmv_launches, 1)
     launches_per_iter = max(st.spmv_launches, 1) / max(min(args.steps, 256), 1)
     achieved = (b_iter / launches_per_iter) / kern_ms / 1e6 if kern_ms > 0 else None
+    # dram bytes per SpMV from the committed ncu capture of THIS kernel build: the entry is used
+    # only if its build tag equals the tag the loaded library reports, else null
     traffic = None
+    build_tag = engine.build_info()
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath)).get(
-                f"s{scale}_{args.dtype}_n{world}" + ("_banded" if banded else ""))
+            ent = json.load(open(tpath)).get(f"s{scale}_{args.dtype}_n{world}_{path}")
+            if ent and ent.get("build") == build_tag:
+                traffic = ent.get("bytes")
         except Exception:
             traffic = None
 
@@ -290,30 +372,30 @@ def run_b200(args, rank, world):
     if rank != 0:
         return
     cpu = None
-    if world == 1 and not args.no_cpu:
-        cpu = cpu_reference_gteps(min(args.cpu_scale, scale), args.dtype)
+    if not args.no_cpu:
+        cs = scale if args.cpu_scale is None else args.cpu_scale
+        cpu = cpu_reference_gteps(cs, args.dtype, bounded_iterations(cs, args.cpu_iterations, 40.0))
+        cpu["same_config"] = cs == scale
     line = {
         "metric": "pagerank_gteps", "value": gteps, "unit": "GTEPS", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": args.dtype,
         "data": "synthetic",
-        "config": {"workload": f"PageRank {args.dtype} on RMAT scale {scale} ef {EDGE_FACTOR} "
-                               f"({nv} V, {ne} E), a/b/c={A}/{B}/{C}, alpha={ALPHA}; "
-                               "a step = one power iteration (one pull-kernel pass over the graph)",
+        "config": {"workload": workload_string(scale, args.dtype),
                    "l2": "inputs larger than L2 (no flush between iterations)" if b_iter > 126e6
                          else "working set fits L2; no flush (dram bytes reported in profiles/)",
                    "partition": "single GPU" if world == 1 else f"2D {rows}x{cols} (row x col comm)",
-                   "pull_path": "banded pre-reduction + tiled pull" if banded else "tiled pull"},
+                   "pull_path": path, "library": build_tag},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": (achieved / peak) if achieved else None, "traffic": traffic,
                      "peak_source": peak_kind,
-                     "kernel": "band_reduce_kernel + pull_tiles_kernel (one SpMV)" if banded
-                               else "pull_tiles_kernel",
+                     "kernel": kernels,
                      "algorithmic_bytes_per_launch": b_iter / launches_per_iter,
                      "kernel_ms_avg": kern_ms, "kernel_share_of_step":
                          (st.spmv_ms / (ms_total * min(args.steps, 256) / args.steps))
                          if ms_total > 0 else None},
         "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": st.gpu_launches, "clocks": clocks,
+        "parity_check": parity,
     }
     if nvlink:
         line["nvlink"] = nvlink

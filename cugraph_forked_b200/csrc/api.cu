@@ -36,6 +36,14 @@ static void fill_device_info(b200_handle* h)
   h->sm_count          = prop.multiProcessorCount;
   h->l2_bytes          = static_cast<size_t>(prop.l2CacheSize);
   h->persisting_l2_max = static_cast<size_t>(prop.persistingL2CacheMaxSize);
+  // random 4/8-byte gathers dominate: a 32-byte L2 fetch granularity halves the DRAM bytes of a
+  // gather that misses (the default fetches 64); B200_L2_FETCH=64|128 restores / widens it
+  {
+    const char* e = std::getenv("B200_L2_FETCH");
+    const size_t g = e ? static_cast<size_t>(std::atoll(e)) : 32;
+    if (g == 32 || g == 64 || g == 128) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, g);
+    cudaGetLastError();
+  }
   B200_EXPECTS(prop.major >= 10, kUnknownError,
                "libcugraph_b200 is built for sm_100a only: no Blackwell GPU on this device.");
   // keep freed blocks in the default pool (dbuf allocates from it, common.cuh); the
@@ -64,7 +72,7 @@ extern "C" {
 
 const char* b200_last_error(void) { return g_last_error.c_str(); }
 
-const char* b200_build_info(void) { return "libcugraph_b200 0.1 (sm_100a, CUDA " B200_STR(CUDART_VERSION) ")"; }
+const char* b200_build_info(void) { return "libcugraph_b200 0.2 (sm_100a, CUDA " B200_STR(CUDART_VERSION) "; spmv sell-r2a)"; }
 
 int b200_handle_create(void* stream, b200_handle_t** out)
 {

@@ -7,6 +7,8 @@
 #include <memory>
 
 #include "centrality.cuh"
+#include "mg_comm.cuh"
+#include "prims.cuh"
 
 namespace b200 {
 namespace capi {
@@ -116,40 +118,117 @@ __global__ void scatter_pairs_kernel(const int32_t* internal, const T* values, s
   }
 }
 
+// Multi-GPU: the (vertex, value) pairs a rank passes may belong to any rank; the reference
+// shuffles them to the owner (shuffle_ext_vertex_value_pairs_to_local_gpu_by_vertex_partitioning,
+// c_api/pagerank.cpp:125-155).  Here all pairs are all-gathered in rank order and every rank keeps
+// the ones it owns, in that order (deterministic).  out_internal = local offsets, or global
+// internal ids (local offset + local_first) when `global_ids`; an id no rank owns is an error.
+template <typename T>
+__global__ void keep_owned_kernel(const int32_t* internal, const uint32_t* pos, const T* values,
+                                  size_t n, int32_t add, int32_t* out_internal, T* out_values)
+{
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+       i += size_t(gridDim.x) * blockDim.x) {
+    if (internal[i] < 0) continue;
+    out_internal[pos[i]] = internal[i] + add;
+    out_values[pos[i]]   = values[i];
+  }
+}
+struct owned_flag { int32_t v; __host__ __device__ operator uint32_t() const { return v >= 0 ? 1u : 0u; } };
+
+inline size_t owned_pairs(b200_handle* h, b200_graph* g, const device_array_view_t* vertices,
+                          const device_array_view_t* values, data_type_id_t value_type,
+                          bool global_ids, dbuf<int32_t>& out_internal, dbuf<char>& out_values)
+{
+  cudaStream_t s = h->stream;
+  size_t n       = vertices->size;
+  B200_EXPECTS(values->size == n, kInvalidInput, "vertex and value arrays differ in size");
+  B200_EXPECTS(values->type == value_type, kInvalidInput,
+               "value type must match the graph's weight type");
+  const size_t vsz = type_size(vertices->type), esz = type_size(value_type);
+  const void* vptr = vertices->data;
+  const void* eptr = values->data;
+  dbuf<char> all_v, all_e;
+  size_t total = n;
+  const bool mg = g->multi_gpu && h->size > 1;
+  if (mg) {
+    std::vector<int64_t> counts64 = allgather_host(h, h->world, h->size, {static_cast<int64_t>(n)});
+    std::vector<size_t> counts(counts64.begin(), counts64.end());
+    total = 0;
+    for (size_t c : counts) total += c;
+    all_v.alloc(std::max<size_t>(total, 1) * vsz, s);
+    all_e.alloc(std::max<size_t>(total, 1) * esz, s);
+    allgatherv(s, h->world, h->size, h->rank, vptr, all_v.data(), counts, vsz);
+    allgatherv(s, h->world, h->size, h->rank, eptr, all_e.data(), counts, esz);
+    vptr = all_v.data();
+    eptr = all_e.data();
+  }
+  dbuf<int32_t> internal(std::max<size_t>(total, 1), s);
+  dbuf<uint32_t> pos(total + 1, s);
+  uint32_t kept = 0;
+  if (total) {
+    graph_ext_to_internal(h, g, vptr, total, internal.data());
+    exclusive_scan<owned_flag, uint32_t>(reinterpret_cast<const owned_flag*>(internal.data()), pos.data(),
+                                         total, s, true);
+    CUDA_TRY(cudaMemcpyAsync(&kept, pos.data() + total, 4, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+  }
+  int64_t kept_all = kept;
+  if (mg) {
+    kept_all = 0;
+    for (int64_t k : allgather_host(h, h->world, h->size, {static_cast<int64_t>(kept)})) kept_all += k;
+  }
+  B200_EXPECTS(kept_all == static_cast<int64_t>(total), kInvalidInput,
+               "Invalid input argument: vertex ids are not in the graph.");
+  out_internal.alloc(std::max<size_t>(kept, 1), s);
+  out_values.alloc(std::max<size_t>(kept, 1) * esz, s);
+  if (total) {
+    const int32_t add = global_ids ? static_cast<int32_t>(g->local_first) : 0;
+    unsigned grid = static_cast<unsigned>(std::min<size_t>((total + 255) / 256, 4096));
+    if (value_type == FLOAT32)
+      keep_owned_kernel<float><<<grid, 256, 0, s>>>(internal.data(), pos.data(),
+                                                   static_cast<const float*>(eptr), total, add,
+                                                   out_internal.data(),
+                                                   reinterpret_cast<float*>(out_values.data()));
+    else
+      keep_owned_kernel<double><<<grid, 256, 0, s>>>(internal.data(), pos.data(),
+                                                    static_cast<const double*>(eptr), total, add,
+                                                    out_internal.data(),
+                                                    reinterpret_cast<double*>(out_values.data()));
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaStreamSynchronize(s));   // the gathered inputs are freed on return
+  }
+  return kept;
+}
+
 inline void collect_dense(b200_handle* h, b200_graph* g, const device_array_view_t* vertices,
                           const device_array_view_t* values, data_type_id_t value_type,
                           dbuf<char>& dense)
 {
   cudaStream_t s = h->stream;
   size_t nloc    = static_cast<size_t>(g->local_last - g->local_first);
-  size_t n       = vertices->size;
-  B200_EXPECTS(values->size == n, kInvalidInput, "vertex and value arrays differ in size");
-  B200_EXPECTS(values->type == value_type, kInvalidInput,
-               "value type must match the graph's weight type");
+  dbuf<int32_t> internal;
+  dbuf<char> vals;
+  const size_t n = owned_pairs(h, g, vertices, values, value_type, false, internal, vals);
   dense.alloc(nloc * type_size(value_type), s);
   CUDA_TRY(cudaMemsetAsync(dense.data(), 0, std::max<size_t>(nloc, 1) * type_size(value_type), s));
-  dbuf<int32_t> internal(n, s);
-  graph_ext_to_internal(h, g, vertices->data, n, internal.data());
   dbuf<int> bad(1, s);
   CUDA_TRY(cudaMemsetAsync(bad.data(), 0, 4, s));
   if (n) {
     unsigned grid = static_cast<unsigned>(std::min<size_t>((n + 255) / 256, 4096));
     if (value_type == FLOAT32)
       scatter_pairs_kernel<float><<<grid, 256, 0, s>>>(internal.data(),
-                                                      static_cast<const float*>(values->data), n,
+                                                      reinterpret_cast<const float*>(vals.data()), n,
                                                       reinterpret_cast<float*>(dense.data()),
                                                       bad.data());
     else
       scatter_pairs_kernel<double><<<grid, 256, 0, s>>>(internal.data(),
-                                                       static_cast<const double*>(values->data), n,
+                                                       reinterpret_cast<const double*>(vals.data()), n,
                                                        reinterpret_cast<double*>(dense.data()),
                                                        bad.data());
     CUDA_TRY(cudaGetLastError());
   }
-  int h_bad = 0;
-  CUDA_TRY(cudaMemcpyAsync(&h_bad, bad.data(), 4, cudaMemcpyDeviceToHost, s));
   CUDA_TRY(cudaStreamSynchronize(s));
-  B200_EXPECTS(!h_bad, kInvalidInput, "Invalid input argument: vertex ids are not in the graph.");
 }
 
 // result = { copy of the renumber map (external ids), scores in internal order }
@@ -580,12 +659,14 @@ static cugraph_error_code_t pagerank_common(
                                nloc * type_size(G->weight_type), cudaMemcpyDeviceToDevice, h->stream));
       p.has_initial_guess = 1;
     }
+    dbuf<char> pers_owned;
     if (pers_vertices) {
-      size_t np = view(pers_vertices)->size;
-      pers_internal.alloc(np, h->stream);
-      graph_ext_to_internal(h, g, view(pers_vertices)->data, np, pers_internal.data());
-      p.personalization_vertices = pers_internal.data();   // -1 entries are rejected by the driver
-      p.personalization_values   = view(pers_values)->data;
+      // the pairs this rank owns, as GLOBAL internal ids (the convention of b200_pagerank on a
+      // multi-GPU graph; on a single GPU local_first is 0)
+      const size_t np = owned_pairs(h, g, view(pers_vertices), view(pers_values), G->weight_type, true,
+                                    pers_internal, pers_owned);
+      p.personalization_vertices = pers_internal.data();
+      p.personalization_values   = pers_owned.data();
       p.personalization_size     = np;
     }
     pagerank(h, g, &p, values->buf.data(), nullptr);

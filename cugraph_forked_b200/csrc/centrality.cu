@@ -420,6 +420,8 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
     Q.cta_partials   = parts;
     Q.slots          = slots;
     Q.state          = state;
+    Q.hot_limit      = static_cast<int32_t>(std::min<int64_t>(
+      ep->num_minors, (static_cast<int64_t>(env_int("B200_HOT_MB", 40)) << 20) / static_cast<int64_t>(sizeof(RT))));
     ++band_launches;
     if (weighted) sell_rows_kernel<RT, true, EPI><<<main_ctas, kSell2Threads, 0, s>>>(Q, epi);
     else          sell_rows_kernel<RT, false, EPI><<<main_ctas, kSell2Threads, 0, s>>>(Q, epi);

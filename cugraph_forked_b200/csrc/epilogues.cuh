@@ -47,6 +47,14 @@ struct epi_raw {
   {
     y[row] = init + scale * sum;
   }
+  // streaming variants (sell.cuh): inputs / outputs that are touched once per iteration bypass
+  // the L2 replacement order (ld.cs / st.cs); outputs of rows < hot_rows are gathered by the next
+  // iteration and are stored normally
+  __device__ __forceinline__ pre_t prefetch_stream(int64_t) const { return {}; }
+  __device__ __forceinline__ void finish_stream(int64_t row, RT sum, pre_t const&, acc2&, int64_t) const
+  {
+    __stcs(y + row, init + scale * sum);
+  }
   __device__ __forceinline__ void operator()(int64_t row, RT sum, acc2& acc) const
   {
     finish(row, sum, prefetch(row), acc);
@@ -117,6 +125,27 @@ struct epi_pagerank {
   {
     finish(row, sum, prefetch(row), acc);
   }
+  __device__ __forceinline__ pre_t prefetch_stream(int64_t row) const
+  {
+    pre_t p;
+    p.old = __ldcs(pr + row);
+    p.sc  = __ldcs(scale + row);
+    p.pv  = pers ? __ldcs(pers + row) : RT(0);
+    return p;
+  }
+  __device__ __forceinline__ void finish_stream(int64_t row, RT sum, pre_t const& p, acc2& acc,
+                                                int64_t hot_rows) const
+  {
+    RT v = sum + unvarying;
+    if (pers) v += pers_factor * p.pv;
+    __stcs(pr + row, v);
+    acc.b += fabs(static_cast<double>(v) - static_cast<double>(p.old));
+    RT xn = RT(0);
+    if (p.sc < RT(0)) acc.a += static_cast<double>(v);
+    else xn = v * p.sc;
+    if (row < hot_rows) x_next[row] = xn;
+    else __stcs(x_next + row, xn);
+  }
 };
 
 // Katz (katz_centrality_impl.cuh:104-148): new = alpha * sum + beta (or betas[v]);
@@ -159,6 +188,22 @@ struct epi_katz {
   {
     finish(row, sum, prefetch(row), acc);
   }
+  __device__ __forceinline__ pre_t prefetch_stream(int64_t row) const
+  {
+    pre_t p;
+    p.old = __ldcs(old_c + row);
+    p.b   = betas ? __ldcs(betas + row) : beta;
+    return p;
+  }
+  __device__ __forceinline__ void finish_stream(int64_t row, RT sum, pre_t const& p, acc2& acc,
+                                                int64_t hot_rows) const
+  {
+    RT v = alpha * sum + p.b;
+    if (row < hot_rows) new_c[row] = v;
+    else __stcs(new_c + row, v);
+    acc.b += fabs(static_cast<double>(v) - static_cast<double>(p.old));
+    acc.a += static_cast<double>(v) * static_cast<double>(v);
+  }
 };
 
 // eigenvector (eigenvector_centrality_impl.cuh:90-135): new = sum; L2 norm accumulated here,
@@ -180,6 +225,13 @@ struct epi_eigen {
   __device__ __forceinline__ void operator()(int64_t row, RT sum, acc2& acc) const
   {
     finish(row, sum, prefetch(row), acc);
+  }
+  __device__ __forceinline__ pre_t prefetch_stream(int64_t) const { return {}; }
+  __device__ __forceinline__ void finish_stream(int64_t row, RT sum, pre_t const&, acc2& acc,
+                                                int64_t) const
+  {
+    new_c[row] = sum;   // normalised (read again) by the driver's vertex pass
+    acc.a += static_cast<double>(sum) * static_cast<double>(sum);
   }
 };
 

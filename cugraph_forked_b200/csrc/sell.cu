@@ -449,12 +449,12 @@ __global__ void sell_p2_fill_kernel(const int32_t* roff, const int32_t* ridx, co
 // task t covers the slices whose cost prefix (entries / 32 + 2 per slice) lies in
 // [t * kSellQ2, (t + 1) * kSellQ2)
 __global__ void sell_p2_tasks_kernel(const uint32_t* sbase, int64_t nslices, int64_t ntasks,
-                                     int32_t* task_first)
+                                     int64_t quantum, int32_t* task_first)
 {
   for (int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; t <= ntasks;
        t += int64_t(gridDim.x) * blockDim.x) {
     if (t == ntasks) { task_first[t] = static_cast<int32_t>(nslices); continue; }
-    const uint64_t target = static_cast<uint64_t>(t) * kSellQ2;
+    const uint64_t target = static_cast<uint64_t>(t) * static_cast<uint64_t>(quantum);
     int64_t lo = 0, hi = nslices;
     while (lo < hi) {
       const int64_t mid = (lo + hi) >> 1;
@@ -631,7 +631,7 @@ static void build_sell(b200_handle* h, edge_partition& ep, const RT* w, sell_lay
     CUDA_TRY(cudaGetLastError());
     // units of consecutive tasks of one band, in band order; sizes follow guided self-scheduling
     const int nctas = h->sm_count;
-    constexpr int64_t kUnitMin = 32, kUnitMax = 1024;
+    const int64_t kUnitMin = T1 >= 64 * int64_t{nctas} ? 32 : 4, kUnitMax = 1024;
     std::vector<band_group> units;
     int band = 0;
     for (int64_t k = 0; k < T1;) {
@@ -729,11 +729,13 @@ static void build_sell(b200_handle* h, edge_partition& ep, const RT* w, sell_lay
     w ? reinterpret_cast<RT*>(L.p2_w.data()) : nullptr, L.p2_row.data());
   CUDA_TRY(cudaGetLastError());
   const int64_t cost = static_cast<int64_t>(p2_rows) + 2 * S2;
-  const int64_t T2   = std::max<int64_t>(1, div_up(cost, kSellQ2));
+  // small graphs: at least ~4 tasks for every warp the kernel can have in flight
+  const int64_t q2   = std::max<int64_t>(8, std::min<int64_t>(kSellQ2, cost / (int64_t{h->sm_count} * 32 * 4)));
+  const int64_t T2   = std::max<int64_t>(1, div_up(cost, q2));
   B200_EXPECTS(T2 < (int64_t{1} << 31) - 1, kUnknownError, "sell layout: too many phase-2 tasks");
   L.p2_num_tasks = T2;
   L.p2_task_first.alloc(static_cast<size_t>(T2) + 1, s);
-  sell_p2_tasks_kernel<<<sgrid(static_cast<size_t>(T2) + 1), kBT, 0, s>>>(L.p2_sbase.data(), S2, T2,
+  sell_p2_tasks_kernel<<<sgrid(static_cast<size_t>(T2) + 1), kBT, 0, s>>>(L.p2_sbase.data(), S2, T2, q2,
                                                                          L.p2_task_first.data());
   CUDA_TRY(cudaGetLastError());
   CUDA_TRY(cudaStreamSynchronize(s));

@@ -29,6 +29,7 @@
 #pragma once
 
 #include "banded.cuh"
+#include "ptx.cuh"
 
 namespace b200 {
 
@@ -39,11 +40,12 @@ constexpr int kSellLong     = 128;    // reduced rows with more entries are chun
 constexpr int kSellWindow   = 1024;   // rows per sort window of phase 2
 constexpr int kSell2Threads = 256;
 #ifndef B200_SELL2_MIN_CTAS
-#define B200_SELL2_MIN_CTAS 6
+#define B200_SELL2_MIN_CTAS 4
 #endif
 constexpr int kSell2MinCtas = B200_SELL2_MIN_CTAS;   // CTAs per SM the phase-2 kernel is compiled for
 constexpr int kSellQ1       = 32;     // phase-1 task quantum: load groups (of 32 * kSellG indices)
-constexpr int kSellQ2       = 96;     // phase-2 task quantum: cost units (32 entries or 1/2 slice)
+constexpr int kSellQ2       = 96;     // largest phase-2 task quantum: cost units (32 entries or 1/2 slice);
+                                      // a task then has < 64 slices (sell_rows_kernel relies on it)
 
 template <typename RT>
 struct sell_geom {
@@ -132,6 +134,7 @@ struct sell_params2 {
   double* cta_partials;
   int32_t slots;
   const iter_state* state;
+  int32_t hot_limit;   // entries [0, hot_limit) of x are kept in L2 (evict_last), the rest streams
 };
 
 // ------------------------------------------------------------------------------------------
@@ -291,6 +294,14 @@ __global__ void __launch_bounds__(kSell2Threads, kSell2MinCtas) sell_rows_kernel
   acc2 acc;
   const RT* x  = P.x;
   const RT* pv = P.pval - P.x_split;   // indexed by the entry itself
+  // L2 replacement order: the head of x (degree-sorted: the sources most rows gather) stays, its
+  // cold tail streams through, the partial sums (eight rows to a line) are ordinary lines
+  const uint64_t pol_hot = policy_evict_last(), pol_cold = policy_evict_first(),
+                 pol_part = policy_evict_normal();
+  auto gather = [&](int32_t i) -> RT {
+    const bool part = i >= P.x_split;
+    return ld_policy((part ? pv : x) + i, part ? pol_part : (i < P.hot_limit ? pol_hot : pol_cold));
+  };
   for (;;) {
     int ti = 0;
     if (lane == 0) ti = atomicAdd(P.queue, 1);
@@ -325,7 +336,7 @@ __global__ void __launch_bounds__(kSell2Threads, kSell2MinCtas) sell_rows_kernel
         n[u]     = static_cast<int>(b[u + 1] - b[u]);
         chunk[u] = sidx < P.chunk_slices;
         const bool live = u == 0 || two;
-        row[u]   = (chunk[u] || !live) ? -1 : __ldg(P.row + static_cast<int64_t>(sidx) * 32 + lane);
+        row[u]   = (chunk[u] || !live) ? -1 : __ldcs(P.row + static_cast<int64_t>(sidx) * 32 + lane);
         ip[u]    = P.idx + static_cast<int64_t>(b[u]) * 32 + lane;
 #pragma unroll
         for (int j = 0; j < 4; ++j)
@@ -336,12 +347,12 @@ __global__ void __launch_bounds__(kSell2Threads, kSell2MinCtas) sell_rows_kernel
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
         pre[u] = typename EPI::pre_t{};
-        if (row[u] >= 0) pre[u] = epi.prefetch(row[u]);
+        if (row[u] >= 0) pre[u] = epi.prefetch_stream(row[u]);
         RT v[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           v[j] = RT(0);
-          if (e[u][j] >= 0) v[j] = __ldg((e[u][j] >= P.x_split ? pv : x) + e[u][j]);
+          if (e[u][j] >= 0) v[j] = gather(e[u][j]);
         }
         if constexpr (WEIGHTED) {
           const RT* wp = P.w + static_cast<int64_t>(b[u]) * 32 + lane;
@@ -361,10 +372,7 @@ __global__ void __launch_bounds__(kSell2Threads, kSell2MinCtas) sell_rows_kernel
           const int32_t i1 = __ldcs(ip[u] + static_cast<int64_t>(j + 1) * 32);
           const int32_t i2 = __ldcs(ip[u] + static_cast<int64_t>(j + 2) * 32);
           const int32_t i3 = __ldcs(ip[u] + static_cast<int64_t>(j + 3) * 32);
-          RT v0 = __ldg((i0 >= P.x_split ? pv : x) + i0);
-          RT v1 = __ldg((i1 >= P.x_split ? pv : x) + i1);
-          RT v2 = __ldg((i2 >= P.x_split ? pv : x) + i2);
-          RT v3 = __ldg((i3 >= P.x_split ? pv : x) + i3);
+          RT v0 = gather(i0), v1 = gather(i1), v2 = gather(i2), v3 = gather(i3);
           if constexpr (WEIGHTED) {
             const RT* wp = P.w + static_cast<int64_t>(b[u]) * 32 + lane;
             v0 *= __ldcs(wp + static_cast<int64_t>(j) * 32);
@@ -376,7 +384,7 @@ __global__ void __launch_bounds__(kSell2Threads, kSell2MinCtas) sell_rows_kernel
         }
         for (; j < n[u]; ++j) {
           const int32_t i0 = __ldcs(ip[u] + static_cast<int64_t>(j) * 32);
-          RT v0 = __ldg((i0 >= P.x_split ? pv : x) + i0);
+          RT v0 = gather(i0);
           if constexpr (WEIGHTED)
             v0 *= __ldcs(P.w + static_cast<int64_t>(b[u]) * 32 + lane + static_cast<int64_t>(j) * 32);
           a0[u] += v0;
@@ -386,7 +394,7 @@ __global__ void __launch_bounds__(kSell2Threads, kSell2MinCtas) sell_rows_kernel
           const int64_t c = static_cast<int64_t>(s_first + k + u) * 32 + lane;
           if ((u == 0 || two) && c < P.num_chunks) P.chunk_partials[c] = static_cast<double>(sum);
         } else if (row[u] >= 0) {
-          epi.finish(row[u], sum, pre[u], acc);
+          epi.finish_stream(row[u], sum, pre[u], acc, P.hot_limit);
         }
       }
     }

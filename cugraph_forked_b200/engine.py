@@ -17,6 +17,11 @@ _DT = {torch.int32: INT32, torch.int64: INT64, torch.float32: FLOAT32, torch.flo
 _TD = {v: k for k, v in _DT.items()}
 
 
+def build_info() -> str:
+    """the library's version / kernel-generation tag (b200_build_info)"""
+    return _lib.lib().b200_build_info().decode()
+
+
 def _ptr(t):
     return None if t is None else ctypes.c_void_p(t.data_ptr())
 

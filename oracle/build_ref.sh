@@ -14,7 +14,7 @@ cxx="${CXX:-g++}"
 # no -march=native: the prebuilt _ref .so must run on whatever host CPU the GPU box has
 flags="-O3 -std=c++17 -fPIC -shared -fno-fast-math -ffp-contract=off"
 
-$cxx $flags -o "$here/libcentrality_oracle.so" "$here/centrality_oracle.cpp"
+$cxx $flags -pthread -o "$here/libcentrality_oracle.so" "$here/centrality_oracle.cpp" "$here/inputs_oracle.cpp"
 
 if [ -d "$ref/cpp/tests" ]; then
   tmp="$(mktemp -d)"

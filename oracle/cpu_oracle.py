@@ -20,8 +20,9 @@ _libs: dict[str, ctypes.CDLL] = {}
 
 
 def build(force: bool = False) -> None:
-    if force or not os.path.exists(_PORT) or (
-        os.path.getmtime(_PORT) < os.path.getmtime(os.path.join(_HERE, "centrality_oracle.cpp"))
+    if force or not os.path.exists(_PORT) or any(
+        os.path.getmtime(_PORT) < os.path.getmtime(os.path.join(_HERE, f))
+        for f in ("centrality_oracle.cpp", "inputs_oracle.cpp")
     ):
         subprocess.check_call(["bash", os.path.join(_HERE, "build_ref.sh")])
 
@@ -196,6 +197,34 @@ def csc_from_coo(src, dst, weights, num_vertices):
     offsets = np.zeros(num_vertices + 1, dtype=np.int64)
     np.cumsum(np.bincount(dst, minlength=num_vertices), out=offsets[1:])
     return offsets, np.asarray(src)[order].astype(np.int32), None if weights is None else np.asarray(weights)[order]
+
+
+def rmat_edgelist_fast(scale, num_edges, a=0.57, b=0.19, c=0.19, seed=0, first_edge=0, threads=0):
+    """graph_oracle.rmat_edgelist (same stream, same bit loop) in C++ on `threads` host threads."""
+    lib = port_lib()
+    src = np.empty(num_edges, np.int32)
+    dst = np.empty(num_edges, np.int32)
+    lib.oracle_rmat_edgelist_i32.restype = None
+    lib.oracle_rmat_edgelist_i32(ctypes.c_int(scale), ctypes.c_int64(num_edges), ctypes.c_double(a),
+                                 ctypes.c_double(b), ctypes.c_double(c), ctypes.c_uint64(seed),
+                                 ctypes.c_uint64(first_edge), _p(src), _p(dst),
+                                 ctypes.c_int(threads or (os.cpu_count() or 1)))
+    return src, dst
+
+
+def csc_from_coo_fast(src, dst, num_vertices, threads=0):
+    """csc_from_coo for unweighted int32 edge lists: stable counting sort by destination in C++."""
+    lib = port_lib()
+    src = np.ascontiguousarray(src, np.int32)
+    dst = np.ascontiguousarray(dst, np.int32)
+    offsets = np.empty(num_vertices + 1, np.int64)
+    indices = np.empty(len(src), np.int32)
+    threads = min(threads or (os.cpu_count() or 1), 16)
+    lib.oracle_csc_from_coo_i32.restype = None
+    lib.oracle_csc_from_coo_i32(_p(src), _p(dst), ctypes.c_int64(len(src)),
+                                ctypes.c_int64(num_vertices), _p(offsets), _p(indices),
+                                ctypes.c_int(threads))
+    return offsets, indices
 
 
 def read_mtx_ref(path, dtype=np.float32):

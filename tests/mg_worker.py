@@ -183,6 +183,55 @@ def run_tiny(handle, rank, world):
     print(f"MG_WORKER_OK rank={rank}/{world} tiny graph: local vertices {len(labels)}", flush=True)
 
 
+def run_c_api(handle, rank, world, scale=10):
+    """cugraph_personalized_pagerank / nstart / precomputed sums through the C API on a
+    multi-GPU graph, with (vertex, value) pairs that belong to OTHER ranks: the library has to
+    move them to their owners (c_api.cu handed local offsets to the MG driver and
+    rejected foreign vertices).  Every rank passes a disjoint slice of the pairs, chosen by
+    position and not by ownership."""
+    from cugraph_forked_b200 import pylibcugraph as plc
+    from tests import util
+    nv, ne = 1 << scale, 16 << scale
+    src, dst = util.rmat(scale, seed=21)
+    # vertex ids appear in the graph only if they have an edge: restrict the pairs to those
+    present = np.zeros(nv, bool)
+    present[src] = True
+    present[dst] = True
+    ids = np.flatnonzero(present).astype(np.int32)
+    relabel = np.cumsum(present) - 1
+    per = ne // world
+    lo, hi = rank * per, (ne if rank == world - 1 else (rank + 1) * per)
+    t = lambda a: torch.as_tensor(np.ascontiguousarray(a)).cuda()
+    rh = plc.ResourceHandle(handle)
+    g = plc.MGGraph(rh, plc.GraphProperties(is_multigraph=True), t(src[lo:hi]), t(dst[lo:hi]),
+                    t(np.ones(hi - lo, np.float64)), store_transposed=True, num_edges=hi - lo)
+    rng = np.random.default_rng(4)
+    pv = rng.permutation(ids)[: len(ids) // 3]
+    pw = rng.random(len(pv)) + 0.1
+    outw = np.bincount(src, minlength=nv).astype(np.float64)
+    guess = rng.random(nv) + 0.5
+    mine = slice(rank, None, world)          # this rank's share of every pair list
+    verts, vals = plc.personalized_pagerank(
+        rh, g, t(ids[mine]), t(outw[ids][mine]), t(ids[mine]), t(guess[ids][mine]), t(pv[mine]),
+        t(pw[mine]), 0.85, 1e-12, 500, False)
+    s2, d2 = relabel[src].astype(np.int32), relabel[dst].astype(np.int32)
+    ref, _ = util.oracle_pagerank(s2, d2, None, len(ids), dtype=np.float64, epsilon=1e-12,
+                                  personalization=(relabel[pv].astype(np.int32), pw),
+                                  initial_guess=guess[ids], max_iterations=500)
+    got = vals.cpu().numpy()
+    err = util.rel_err(got, ref[relabel[verts.cpu().numpy()]]).max() if len(got) else 0.0
+    assert err <= 1e-8, f"MG C-API personalized PageRank differs: {err:.3e}"
+    # an id no rank owns is rejected on every rank
+    bad = np.array([nv + 7], np.int32) if rank == 0 else np.zeros(0, np.int32)
+    try:
+        plc.personalized_pagerank(rh, g, None, None, None, None, t(bad), t(np.ones(len(bad))), 0.85,
+                                  1e-6, 100, False)
+        raise AssertionError("a vertex outside the graph was accepted")
+    except (RuntimeError, ValueError) as e:
+        assert "not in the graph" in str(e)
+    print(f"MG_WORKER_OK rank={rank}/{world} C API pairs shuffled to owners: err={err:.2e}", flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--scale", type=int, default=12)
@@ -198,6 +247,7 @@ def main():
     for dtype, weighted in ((np.float32, False), (np.float64, True), (np.float32, True)):
         run(args.scale, args.edge_factor, dtype, weighted, handle, rank, world)
     run_tiny(handle, rank, world)
+    run_c_api(handle, rank, world)
     # a graph with long rows in every partition (hubs) and many empty rows
     run(args.scale + 2, 8, np.float32, False, handle, rank, world)
 

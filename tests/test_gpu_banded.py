@@ -1,4 +1,6 @@
-"""GPU parity of the two-phase banded path (cugraph_forked_b200/csrc/banded.cu[h]): the same
+"""GPU parity of the two-phase pull path - the round-2 default "lane owns a segment" layout
+(csrc/sell.cu[h], B200_LAYOUT=2) and the round-1 banded layout kept as a fallback
+(csrc/banded.cu[h], B200_LAYOUT=1): the same
 oracle comparisons as test_gpu_centrality.py with B200_BANDED=1, plus agreement with the
 single-phase kernel and a torch fp64 segmented sum.  `st.gpu_launches >= 3 * iterations`
 (band + tiles + tail per iteration) proves the banded kernels actually ran."""
@@ -12,9 +14,10 @@ from tests.test_gpu_centrality import TDT, _check_pagerank, _graph
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(autouse=True)
-def banded_on(monkeypatch):
+@pytest.fixture(autouse=True, params=["2", "1"], ids=["sell", "banded-r1"])
+def banded_on(monkeypatch, request):
     monkeypatch.setenv("B200_BANDED", "1")
+    monkeypatch.setenv("B200_LAYOUT", request.param)
 
 
 def _dense_ref(g, x, weighted):

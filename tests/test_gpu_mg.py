@@ -41,7 +41,7 @@ def test_mg_world_size_1_banded(mg1, monkeypatch, capfd, dtype, weighted):
     monkeypatch.setenv("B200_BAND_HOT_MIN", "1024")
     monkeypatch.setenv("B200_BAND_VERBOSE", "1")
     mg_worker.run(15, 16, dtype, weighted, mg1, 0, 1, verbose=False)
-    assert "banded layout" in capfd.readouterr().err
+    assert "sell layout" in capfd.readouterr().err
 
 
 def test_mg_tiny_graph_world_size_1(mg1):
@@ -80,11 +80,11 @@ def test_mg_torchrun(world, oracle_built):
            str(29500 + world), os.path.join(ROOT, "tests", "mg_worker.py"), "--scale", "12"]
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=900)
     ok = r.stdout.count("MG_WORKER_OK")
-    assert r.returncode == 0 and ok == 5 * world, (r.stdout[-3000:], r.stderr[-3000:])
+    assert r.returncode == 0 and ok == 6 * world, (r.stdout[-3000:], r.stderr[-3000:])
     # again with the banded pre-reduction forced onto the small partitions
     env = dict(os.environ, B200_BANDED="1", B200_BAND_MIN_EDGES="512", B200_BAND_HOT_MIN="64",
                B200_BAND_VERBOSE="1")
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=900, env=env)
     ok = r.stdout.count("MG_WORKER_OK")
-    assert r.returncode == 0 and ok == 5 * world, (r.stdout[-3000:], r.stderr[-3000:])
-    assert "banded layout" in r.stderr
+    assert r.returncode == 0 and ok == 6 * world, (r.stdout[-3000:], r.stderr[-3000:])
+    assert "sell layout" in r.stderr
