@@ -254,7 +254,7 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
   // opt-in fused rectangle keeps the single-phase kernel
   const bool is_fused = !g->fused.empty() && ep == &g->fused[0];
   sell = nullptr;
-  if (tiled && !is_fused && !ep->offsets64 && env_int("B200_BANDED", kBandedDefault) != 0 &&
+  if (tiled && !ep->offsets64 && env_int("B200_BANDED", kBandedDefault) != 0 &&
       env_int("B200_LAYOUT", 2) == 2) {
     sell_layout* sl = sell_get<RT>(h, *ep, weights);
     if (sl && sl->enabled) {
@@ -322,7 +322,10 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
     sell_ctas1 = h->sm_count;
     int per_sm = std::max(1, env_int("B200_SELL_CTAS_PER_SM", 8));
     if (g->multi_gpu && h->size > 1) {
-      sell_ctas1 = std::max(1, sell_ctas1 - std::max(0, env_int("B200_MG_RESERVED_SMS", 16)));
+      // per-partition launches overlap the previous partition's reduction (NCCL needs SMs of its
+      // own: these kernels fill the register file); the fused rectangle overlaps only the deferred
+      // 2-scalar allreduce of the previous iteration
+      sell_ctas1 = std::max(1, sell_ctas1 - std::max(0, env_int("B200_MG_RESERVED_SMS", is_fused ? 4 : 16)));
     }
     main_ctas = sell_ctas1 * per_sm;   // phase-2 grid: 256-thread CTAs, tasks claimed dynamically
     int64_t want_tail = div_up(std::max<int64_t>(sell->num_long_rows, 1), 32);

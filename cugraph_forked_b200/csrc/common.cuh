@@ -163,6 +163,7 @@ struct b200_handle {
   int rank{0}, size{1};
   int row_size{1}, col_size{1};   // R, C
   int row_rank{0}, col_rank{0};   // rank inside row_comm / col_comm
+  std::shared_ptr<void> peer;     // mg_peer.cuh: IPC-mapped exchange heap of the box's ranks
 };
 
 namespace b200 {
@@ -228,6 +229,7 @@ struct b200_graph {
   // per-partition copies above are what the views and the parity tests read.
   std::vector<b200::edge_partition> fused;      // 0 or 1 entries
   std::vector<int64_t> fused_row_first;         // size C + 1: rows of partition i inside `fused`
+  int64_t fused_slice{0};                        // rows per partition slice of `fused` (padded, equal)
   int64_t segment_offsets[8]{};
   int num_segments{0};
   // cached out-weight sums (double precision master copy, local vertices)

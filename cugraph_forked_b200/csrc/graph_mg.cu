@@ -186,6 +186,24 @@ __global__ void partition_offsets_kernel(const unsigned long long* row_start, in
     offsets[r] = static_cast<ET>(row_start[row_first + r] - base);
 }
 
+// offsets of the fused rectangle: partition i's rows start at row i * slice (slice = the largest
+// major range, so that the C partial-sum slices have one size and ONE reduce-scatter combines
+// them); the rows behind a partition's last major are empty
+template <typename ET>
+__global__ void fused_offsets_kernel(const unsigned long long* row_start, const int64_t* piece_first,
+                                     int C, int64_t slice, ET* offsets)
+{
+  const int64_t total = static_cast<int64_t>(C) * slice;
+  for (int64_t r = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; r <= total;
+       r += int64_t(gridDim.x) * blockDim.x) {
+    const int64_t i = r == total ? C - 1 : r / slice;
+    int64_t k       = r - i * slice;
+    const int64_t n = piece_first[i + 1] - piece_first[i];
+    if (k > n) k = n;
+    offsets[r] = static_cast<ET>(row_start[piece_first[i] + k]);
+  }
+}
+
 __global__ void add_u64_to_double_kernel(const unsigned long long* in, size_t n, double* out)
 {
   for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
@@ -594,16 +612,23 @@ static void create_mg_t(b200_handle* h, const VT* src, const VT* dst, const void
     ep.seg[0] = 0; ep.seg[1] = seg[1]; ep.seg[2] = seg[2]; ep.seg[3] = seg[nseg - 2];
     ep.seg[4] = ep.num_rows;
   }
-  // ---- 9. (opt-in, B200_MG_FUSED=1) the same edges once more as a single rectangle over the
-  //         concatenated major ranges: one launch per iteration instead of C; see mg.cu for
-  //         the measurement that keeps it off by default ----
+  // ---- 9. (default since round 2; B200_MG_FUSED=0 turns it off) the same edges once more as a
+  //         single rectangle over the concatenated major ranges: one launch train and one
+  //         grouped reduction per iteration instead of C of each; see mg.cu ----
   g->fused.clear();
   g->fused_row_first.assign(major_piece_first.begin(), major_piece_first.end());
+  g->fused_slice = 0;
   const char* want_fused = std::getenv("B200_MG_FUSED");
-  if (C > 1 && want_fused && std::atoi(want_fused) != 0) {
+  if (C > 1 && (want_fused ? std::atoi(want_fused) != 0 : true)) {
+    int64_t slice = 0;
+    for (int i = 0; i < C; ++i) slice = std::max<int64_t>(slice, static_cast<int64_t>(major_counts[i]));
+    slice = (slice + 31) & ~int64_t{31};
+    g->fused_slice = slice;
+    for (int i = 0; i <= C; ++i) g->fused_row_first[i] = i * slice;
+    const int64_t n_rows_f = slice * C;
     g->fused.resize(1);
     edge_partition& fp = g->fused[0];
-    fp.num_rows    = n_major;
+    fp.num_rows    = n_rows_f;
     fp.num_edges   = static_cast<int64_t>(ne);
     fp.major_first = -1;  // not one global range
     fp.minor_first = minor_first;
@@ -626,20 +651,24 @@ static void create_mg_t(b200_handle* h, const VT* src, const VT* dst, const void
           reinterpret_cast<double*>(fp.weights.data()));
       CUDA_TRY(cudaGetLastError());
     }
-    const size_t nr = static_cast<size_t>(n_major);
+    const size_t nr = static_cast<size_t>(n_rows_f);
+    dbuf<int64_t> d_piece(static_cast<size_t>(C) + 1, s);
+    CUDA_TRY(cudaMemcpyAsync(d_piece.data(), major_piece_first.data(), (static_cast<size_t>(C) + 1) * 8,
+                             cudaMemcpyHostToDevice, s));
     if (fp.offsets64) {
       fp.offsets.alloc((nr + 1) * 8, s, 64);
-      partition_offsets_kernel<int64_t><<<grid_for(nr + 1, 4), kThreads, 0, s>>>(
-        row_start.data(), 0, n_major, reinterpret_cast<int64_t*>(fp.offsets.data()));
+      fused_offsets_kernel<int64_t><<<grid_for(nr + 1, 4), kThreads, 0, s>>>(
+        row_start.data(), d_piece.data(), C, slice, reinterpret_cast<int64_t*>(fp.offsets.data()));
     } else {
       fp.offsets.alloc((nr + 1) * 4, s, 64);
-      partition_offsets_kernel<int32_t><<<grid_for(nr + 1, 4), kThreads, 0, s>>>(
-        row_start.data(), 0, n_major, reinterpret_cast<int32_t*>(fp.offsets.data()));
+      fused_offsets_kernel<int32_t><<<grid_for(nr + 1, 4), kThreads, 0, s>>>(
+        row_start.data(), d_piece.data(), C, slice, reinterpret_cast<int32_t*>(fp.offsets.data()));
     }
     CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaStreamSynchronize(s));   // d_piece is freed at the end of this scope
     fp.has_segments     = true;
     fp.generic_schedule = true;
-    fp.seg[4]           = n_major;
+    fp.seg[4]           = n_rows_f;
   }
   CUDA_TRY(cudaStreamSynchronize(s));
 

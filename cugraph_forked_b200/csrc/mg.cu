@@ -16,6 +16,7 @@
 
 #include "centrality.cuh"
 #include "mg_comm.cuh"
+#include "mg_peer.cuh"
 #include "prims.cuh"
 
 namespace b200 {
@@ -269,6 +270,89 @@ struct mg_engine {
   std::vector<dbuf<RT>> partial;      // one result buffer per local edge partition
   dbuf<RT> x_minor;                   // gathered vector over the local minor range
   dbuf<RT> sum;                       // reduced result for the local vertices
+  dbuf<RT> sum_padded;                // fused path: this rank's (padded) slice after the reduce-scatter
+  // peer-memory exchange (mg_peer.cuh): partial sums and the gathered vector go through an
+  // IPC-mapped heap, double-buffered
+  bool p2p{false};
+  peer_heap* heap{nullptr};
+  size_t off_part[2]{0, 0}, off_x[2]{0, 0};
+  int buf{0};
+  dbuf<uint64_t*> d_slots_row, d_slots_col;
+  dbuf<const RT*> d_srcs[2];
+  dbuf<double*> d_val_slots[2];
+  dbuf<uint64_t*> d_flag_slots;
+  RT* part_local(int b) const { return heap->at<RT>(h->rank, off_part[b]); }
+  void peer_barrier(bool col)
+  {
+    const uint64_t epoch = col ? ++heap->epoch_col : ++heap->epoch_row;
+    peer_barrier_kernel<<<1, 32, 0, h->stream>>>(
+      col ? d_slots_col.data() : d_slots_row.data(),
+      heap->at<uint64_t>(h->rank, peer_heap::flag_offset(col, 0)), col ? C : R, epoch, heap->d_error);
+    CUDA_TRY(cudaGetLastError());
+    ++launches;
+  }
+  void setup_p2p()
+  {
+    cudaStream_t s = h->stream;
+    // one layout for every rank of the box: sizes are the maxima over the world
+    std::vector<int64_t> all = allgather_host(
+      h, h->world, h->size, {static_cast<int64_t>(g->fused_slice) * C, static_cast<int64_t>(nloc)});
+    int64_t max_part = 0, max_x = 0;
+    for (int p = 0; p < h->size; ++p) {
+      max_part = std::max(max_part, all[2 * p]);
+      max_x    = std::max(max_x, all[2 * p + 1]);
+    }
+    const size_t pb = (static_cast<size_t>(max_part) * sizeof(RT) + 255) & ~size_t{255};
+    const size_t xb = (static_cast<size_t>(max_x) * sizeof(RT) + 255) & ~size_t{255};
+    heap        = peer_heap_get(h, 2 * pb + 2 * xb);
+    off_part[0] = kPeerHeader;
+    off_part[1] = kPeerHeader + pb;
+    off_x[0]    = kPeerHeader + 2 * pb;
+    off_x[1]    = kPeerHeader + 2 * pb + xb;
+    // world rank of row peer j / column peer t (partition_manager.hpp:86-103)
+    auto row_peer = [&](int j) { return (h->rank / R) * R + j; };
+    auto col_peer = [&](int t) { return t * R + (h->rank % R); };
+    std::vector<uint64_t*> sr(R), sc(C);
+    for (int j = 0; j < R; ++j)
+      sr[j] = heap->at<uint64_t>(row_peer(j), peer_heap::flag_offset(false, h->row_rank));
+    for (int t = 0; t < C; ++t)
+      sc[t] = heap->at<uint64_t>(col_peer(t), peer_heap::flag_offset(true, h->col_rank));
+    d_slots_row.alloc(R, s);
+    d_slots_col.alloc(C, s);
+    CUDA_TRY(cudaMemcpyAsync(d_slots_row.data(), sr.data(), R * sizeof(void*), cudaMemcpyHostToDevice, s));
+    CUDA_TRY(cudaMemcpyAsync(d_slots_col.data(), sc.data(), C * sizeof(void*), cudaMemcpyHostToDevice, s));
+    for (int b = 0; b < 2; ++b) {
+      std::vector<const RT*> src(C);
+      for (int t = 0; t < C; ++t)
+        src[t] = heap->at<RT>(col_peer(t), off_part[b]) + static_cast<size_t>(h->col_rank) * g->fused_slice;
+      d_srcs[b].alloc(C, s);
+      CUDA_TRY(cudaMemcpyAsync(d_srcs[b].data(), src.data(), C * sizeof(void*), cudaMemcpyHostToDevice, s));
+      CUDA_TRY(cudaStreamSynchronize(s));
+    }
+    {
+      std::vector<uint64_t*> fs(h->size);
+      for (int t = 0; t < h->size; ++t) fs[t] = heap->at<uint64_t>(t, peer_heap::scal_flag_offset(h->rank));
+      d_flag_slots.alloc(h->size, s);
+      CUDA_TRY(cudaMemcpyAsync(d_flag_slots.data(), fs.data(), h->size * sizeof(void*), cudaMemcpyHostToDevice, s));
+      for (int par = 0; par < 2; ++par) {
+        std::vector<double*> vs(h->size);
+        for (int t = 0; t < h->size; ++t) vs[t] = heap->at<double>(t, peer_heap::scal_val_offset(par, h->rank));
+        d_val_slots[par].alloc(h->size, s);
+        CUDA_TRY(cudaMemcpyAsync(d_val_slots[par].data(), vs.data(), h->size * sizeof(void*),
+                                 cudaMemcpyHostToDevice, s));
+        CUDA_TRY(cudaStreamSynchronize(s));
+      }
+    }
+    CUDA_TRY(cudaStreamSynchronize(s));
+  }
+  void check_peer_error()
+  {
+    if (!p2p) return;
+    int e = 0;
+    CUDA_TRY(cudaMemcpyAsync(&e, heap->d_error, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    B200_EXPECTS(e == 0, kUnknownError, "multi-GPU exchange: a peer did not reach the barrier (timeout)");
+  }
   std::vector<size_t> row_counts;     // vertex partition sizes of the row_comm peers
   dbuf<iter_state> state;
   dbuf<double> partials;              // [2][vg]
@@ -295,7 +379,7 @@ struct mg_engine {
   }
   void print_trace()
   {
-    if (!trace || h->rank != 0) return;
+    if (!trace || (h->rank != 0 && env_int("B200_MG_TRACE", 0) < 2)) return;
     size_t iters = ev_trace.size() / 5;
     if (iters == 0) return;
     double acc[4] = {0, 0, 0, 0};
@@ -306,9 +390,9 @@ struct mg_engine {
         acc[k] += ms;
       }
     fprintf(stderr,
-            "[b200 mg trace] %zu iterations: allgather %.1f us, partition kernels %.1f us, "
+            "[b200 mg trace] rank %d: %zu iterations: allgather %.1f us, partition kernels %.1f us, "
             "reduce tail %.1f us, vertex pass + allreduce %.1f us\n",
-            iters, 1e3 * acc[0] / iters, 1e3 * acc[1] / iters, 1e3 * acc[2] / iters,
+            h->rank, iters, 1e3 * acc[0] / iters, 1e3 * acc[1] / iters, 1e3 * acc[2] / iters,
             1e3 * acc[3] / iters);
   }
 
@@ -320,17 +404,23 @@ struct mg_engine {
     nloc           = static_cast<size_t>(g->local_last - g->local_first);
     n_minor        = static_cast<size_t>(g->parts[0].num_minors);
     int vt         = sizeof(RT) == 4 ? B200_FLOAT32 : B200_FLOAT64;
-    // One launch over all local partitions (B200_MG_FUSED=1, also read at graph creation) was
-    // measured against the default of one launch per partition whose reduction overlaps the
-    // next kernel: at 8 GPUs / scale 24 the fused kernel is 17 % faster but its C reductions
-    // no longer overlap anything (118 vs 41 us), 545 vs 585 GTEPS overall - so it is opt-in.
-    fused = !g->fused.empty() && env_int("B200_MG_FUSED", 0) != 0;
+    // One launch train over all local partitions (B200_MG_FUSED, also read at graph creation).
+    // Round 1 measured it against one launch per partition whose reduction overlaps the next
+    // kernel and kept it opt-in (its single-phase kernel was 17 % faster at 8 GPUs / scale 24,
+    // but the C reductions no longer overlapped: 545 vs 585 GTEPS).  With the round-2 layout
+    // (sell.cuh) the per-partition rectangles of an 8-GPU grid are too small to fill the
+    // kernels (3 launches x C per iteration at the efficiency of a scale-20 graph), so the
+    // fused rectangle is the default; profiles/r2_notes.md has the per-phase times.
+    fused = !g->fused.empty() && env_int("B200_MG_FUSED", 1) != 0;
     if (fused) {
       // one launch over all local partitions; partial sums of partition i are the rows
       // [fused_row_first[i], fused_row_first[i + 1]) of one result buffer
       parts.assign(1, partition_spmv_create(h, g, -1, vt));
       partial.resize(1);
-      partial[0].alloc(static_cast<size_t>(g->fused[0].num_rows), s, 8);
+      sum_padded.alloc(static_cast<size_t>(g->fused_slice), s, 8);
+      p2p = env_int("B200_MG_P2P", 1) != 0;
+      if (p2p) setup_p2p();
+      else partial[0].alloc(static_cast<size_t>(g->fused[0].num_rows), s, 8);
     } else {
       parts.assign(C, nullptr);
       for (int i = 0; i < C; ++i) parts[i] = partition_spmv_create(h, g, i, vt);
@@ -369,7 +459,22 @@ struct mg_engine {
   {
     cudaStream_t s = h->stream;
     mark(0);
-    allgatherv(s, h->row, R, h->row_rank, x_local, x_minor.data(), row_counts, sizeof(RT));
+    if (p2p && R > 1) {
+      // publish the local slice, wait for the row peers, copy their slices out of their heaps
+      std::vector<size_t> dis(R + 1, 0);
+      for (int j = 0; j < R; ++j) dis[j + 1] = dis[j] + row_counts[j];
+      RT* mine = heap->at<RT>(h->rank, off_x[buf]);
+      if (nloc) CUDA_TRY(cudaMemcpyAsync(mine, x_local, nloc * sizeof(RT), cudaMemcpyDeviceToDevice, s));
+      peer_barrier(false);
+      for (int j = 0; j < R; ++j) {
+        if (!row_counts[j]) continue;
+        const RT* from = j == h->row_rank ? x_local : heap->at<RT>((h->rank / R) * R + j, off_x[buf]);
+        CUDA_TRY(cudaMemcpyAsync(x_minor.data() + dis[j], from, row_counts[j] * sizeof(RT),
+                                 cudaMemcpyDefault, s));
+      }
+    } else {
+      allgatherv(s, h->row, R, h->row_rank, x_local, x_minor.data(), row_counts, sizeof(RT));
+    }
     mark(1);
     const bool time_it = timed < 256;
     if (time_it) {
@@ -381,21 +486,35 @@ struct mg_engine {
       CUDA_TRY(cudaEventRecord(a, s));
     }
     if (fused) {
-      partition_spmv_run(parts[0], x_minor.data(), partial[0].data(), state.data());
+      RT* part = p2p ? part_local(buf) : partial[0].data();
+      partition_spmv_run(parts[0], x_minor.data(), part, state.data());
       if (time_it) {
         CUDA_TRY(cudaEventRecord(ev_time[2 * timed + 1], s));
         ++timed;
       }
       mark(2);
-      // every partition's partial sums go to the col_comm rank that owns those majors
-      NCCL_TRY(ncclGroupStart());
-      for (int i = 0; i < C; ++i) {
-        size_t cnt = static_cast<size_t>(g->parts[i].num_rows);
-        if (cnt)
-          NCCL_TRY(ncclReduce(partial[0].data() + g->fused_row_first[i], sum.data(), cnt,
-                              nccl_type<RT>::value, ncclSum, i, h->col, s));
+      if (p2p) {
+        // every column peer has written its partial sums: sum the C copies of this rank's slice
+        // (C - 1 of them over NVLink) in column-rank order
+        peer_barrier(true);
+        const size_t n     = static_cast<size_t>(g->fused_slice);
+        const unsigned grd = static_cast<unsigned>(std::min<size_t>((n / (16 / sizeof(RT)) + 255) / 256 + 1,
+                                                                    size_t(h->sm_count) * 8));
+        if (C == 2)      peer_reduce_kernel<RT, 2><<<grd, 256, 0, s>>>(d_srcs[buf].data(), sum_padded.data(), n);
+        else if (C == 4) peer_reduce_kernel<RT, 4><<<grd, 256, 0, s>>>(d_srcs[buf].data(), sum_padded.data(), n);
+        else if (C == 8) peer_reduce_kernel<RT, 8><<<grd, 256, 0, s>>>(d_srcs[buf].data(), sum_padded.data(), n);
+        else B200_EXPECTS(false, kNotImplemented, "peer reduction: unsupported column count");
+        CUDA_TRY(cudaGetLastError());
+        ++launches;
+        buf ^= 1;
+        mark(3);
+        return;
       }
-      NCCL_TRY(ncclGroupEnd());
+      // B200_MG_P2P=0: ONE reduce-scatter on the column communicator (the C slices of the fused
+      // result have one padded size)
+      NCCL_TRY(ncclReduceScatter(partial[0].data(), sum_padded.data(),
+                                 static_cast<size_t>(g->fused_slice), nccl_type<RT>::value, ncclSum,
+                                 h->col, s));
       mark(3);
       return;
     }
@@ -420,7 +539,7 @@ struct mg_engine {
     }
     mark(3);
   }
-  const RT* result() const { return C == 1 ? partial[0].data() : sum.data(); }
+  const RT* result() const { return C == 1 ? partial[0].data() : (fused ? sum_padded.data() : sum.data()); }
 
   // scal = allreduce(fold(partials)); then commit into the state.  With `deferred` the
   // allreduce and the commit run on the second stream and the caller joins them with
@@ -432,6 +551,19 @@ struct mg_engine {
                       bool deferred = false)
   {
     cudaStream_t s = h->stream;
+    if (p2p) {
+      const uint64_t epoch = ++heap->epoch_scal;
+      const int par        = static_cast<int>(epoch & 1);
+      peer_scalars_kernel<<<1, 256, 0, s>>>(
+        partials.data(), static_cast<int>(vg), d_val_slots[par].data(), d_flag_slots.data(),
+        heap->at<double>(h->rank, peer_heap::scal_val_offset(par, 0)),
+        heap->at<uint64_t>(h->rank, peer_heap::scal_flag_offset(0)), h->size, epoch, state.data(),
+        threshold, iteration, check ? 1 : 0, which, heap->d_error);
+      CUDA_TRY(cudaGetLastError());
+      launches += 1;
+      if (iteration > 0) mark(4);
+      return;
+    }
     mg_fold_kernel<<<1, 256, 0, s>>>(partials.data(), static_cast<int>(vg), state.data(), scal.data());
     CUDA_TRY(cudaGetLastError());
     cudaStream_t cs = s;
@@ -469,6 +601,7 @@ struct mg_engine {
     iter_state hs;
     CUDA_TRY(cudaMemcpyAsync(&hs, state.data(), sizeof hs, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
+    check_peer_error();
     return hs;
   }
 

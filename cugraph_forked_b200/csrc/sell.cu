@@ -50,12 +50,13 @@ __global__ void sell_row_starts_kernel(const int32_t* off, int64_t n_rows, uint8
 }
 
 // f8[e]: bit 0 row start (input), bit 1 cell start (output)
-__global__ void sell_cell_starts_kernel(const int32_t* idx, int64_t ne, int band_entries, uint8_t* f8)
+__global__ void sell_cell_starts_kernel(const int32_t* idx, int64_t ne, int band_entries, int cell_max,
+                                        uint8_t* f8)
 {
   for (int64_t e = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; e < ne;
        e += int64_t(gridDim.x) * blockDim.x) {
     const uint8_t rs = f8[e] & 1u;
-    bool f = rs || e == 0 || (e % kSellCellMax) == 0;
+    bool f = rs || e == 0 || (e % cell_max) == 0;
     if (!f) f = (idx[e] / band_entries) != (idx[e - 1] / band_entries);
     f8[e] = static_cast<uint8_t>(rs | (f ? 2u : 0u));
   }
@@ -161,7 +162,8 @@ __global__ void sell_reduced_offsets_kernel(const int32_t* off, int64_t n, const
 // one record per pre-reduced cell, at its partial slot q (row-major): first edge, and the sort
 // key (band << 32 | kSellCellMax - length); total[0] += edges of pre-reduced cells
 __global__ void sell_cell_records_kernel(const uint8_t* m8, const uint32_t* pid, const int32_t* idx,
-                                         int64_t ne, int band_entries, uint32_t* ce0, uint64_t* keys,
+                                         int64_t ne, int band_entries, int cell_max, uint32_t* ce0,
+                                         uint64_t* keys,
                                          uint32_t* vals, unsigned long long* total)
 {
   unsigned long long mine = 0;
@@ -173,7 +175,7 @@ __global__ void sell_cell_records_kernel(const uint8_t* m8, const uint32_t* pid,
     const uint32_t q = pid[e];
     ce0[q]  = static_cast<uint32_t>(e);
     keys[q] = (static_cast<uint64_t>(static_cast<uint32_t>(idx[e] / band_entries)) << 32) |
-              static_cast<uint64_t>(kSellCellMax - len);
+              static_cast<uint64_t>(cell_max - len);
     vals[q] = q;
     mine += static_cast<unsigned long long>(len);
   }
@@ -209,13 +211,13 @@ __device__ __forceinline__ int sell_band_of_slice(const int64_t* slice_first, in
 // load groups of every phase-1 slice = ceil(length of its first (longest) cell / kSellG)
 __global__ void sell_p1_groups_kernel(const uint64_t* keys, const int64_t* bstart,
                                       const int64_t* slice_first, int nb, int64_t nslices,
-                                      uint32_t* groups)
+                                      int cell_max, uint32_t* groups)
 {
   for (int64_t s = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; s < nslices;
        s += int64_t(gridDim.x) * blockDim.x) {
     const int k      = sell_band_of_slice(slice_first, nb, s);
     const int64_t c0 = bstart[k] + (s - slice_first[k]) * 32;
-    const int len    = kSellCellMax - static_cast<int>(keys[c0] & 0xffffffffu);
+    const int len    = cell_max - static_cast<int>(keys[c0] & 0xffffffffu);
     groups[s]        = static_cast<uint32_t>((len + kSellG - 1) / kSellG);
   }
 }
@@ -226,8 +228,8 @@ template <typename RT>
 __global__ void sell_p1_fill_kernel(const uint64_t* keys, const uint32_t* vals, const uint32_t* ce0,
                                     const int64_t* bstart, const int64_t* slice_first, int nb,
                                     int64_t nslices, const uint32_t* sbase, const int32_t* idx,
-                                    const RT* w, int band_entries, uint16_t* out_idx, RT* out_w,
-                                    int32_t* out_slot, uint32_t* inv)
+                                    const RT* w, int band_entries, int cell_max, uint16_t* out_idx,
+                                    RT* out_w, int32_t* out_slot, uint32_t* inv)
 {
   const int lane = threadIdx.x & 31;
   const int64_t warp0 = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5;
@@ -240,7 +242,7 @@ __global__ void sell_p1_fill_kernel(const uint64_t* keys, const uint32_t* vals, 
     int64_t e0 = 0;
     int32_t slot = -1;
     if (live) {
-      len  = kSellCellMax - static_cast<int>(keys[c] & 0xffffffffu);
+      len  = cell_max - static_cast<int>(keys[c] & 0xffffffffu);
       slot = static_cast<int32_t>(vals[c]);
       e0   = ce0[slot];
       if (inv) {   // band-major partial slots: the cell's rank in the sorted order
@@ -275,7 +277,8 @@ __global__ void sell_p1_fill_kernel(const uint64_t* keys, const uint32_t* vals, 
 // phase-1 task t of band k covers the slices whose first load group lies in
 // [gfirst + t * kSellQ1, gfirst + (t + 1) * kSellQ1), gfirst = first group of the band
 __global__ void sell_p1_tasks_kernel(const int64_t* task_first_of_band, const int64_t* slice_first,
-                                     int nb, const uint32_t* sbase, int64_t ntasks, sell_task* tasks)
+                                     int nb, const uint32_t* sbase, int64_t ntasks, int64_t quantum,
+                                     sell_task* tasks)
 {
   for (int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; t < ntasks;
        t += int64_t(gridDim.x) * blockDim.x) {
@@ -284,7 +287,7 @@ __global__ void sell_p1_tasks_kernel(const int64_t* task_first_of_band, const in
     const uint32_t gfirst = sbase[s0];
     auto first_slice = [&](int64_t tt) {
       // first slice in [s0, s1] with sbase[s] >= gfirst + tt * kSellQ1
-      const uint64_t target = static_cast<uint64_t>(gfirst) + static_cast<uint64_t>(tt) * kSellQ1;
+      const uint64_t target = static_cast<uint64_t>(gfirst) + static_cast<uint64_t>(tt) * static_cast<uint64_t>(quantum);
       int64_t lo = s0, hi = s1;
       while (lo < hi) {
         const int64_t mid = (lo + hi) >> 1;
@@ -468,6 +471,11 @@ __global__ void sell_p2_tasks_kernel(const uint32_t* sbase, int64_t nslices, int
 }  // namespace
 
 namespace {
+inline int env_int_or(const char* name, int dflt)
+{
+  const char* e = std::getenv(name);
+  return e ? std::atoi(e) : dflt;
+}
 __global__ void sell_gather_u32_kernel(const uint32_t* src, const int64_t* at, int n, uint32_t* out)
 {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
@@ -494,6 +502,10 @@ static void build_sell(b200_handle* h, edge_partition& ep, const RT* w, sell_lay
     return;
   CUDA_TRY(cudaStreamSynchronize(s));
   const auto t_begin = std::chrono::steady_clock::now();
+  // cells are cut at CSC positions that are multiples of cell_max: long cells keep the partial
+  // count of the hub rows down (large graphs), short ones keep a lane's longest walk - one task -
+  // short enough for the CTAs of a small graph to finish together (profiles/r2_notes.md)
+  const int cell_max = env_int_or("B200_SELL_CELL_MAX", ne >= (int64_t{1} << 29) ? kSellCellMax : 128);
   const int32_t* off = reinterpret_cast<const int32_t*>(ep.offsets.data());
   const int32_t* idx = ep.indices.data();
   const size_t n     = static_cast<size_t>(ne);
@@ -506,7 +518,7 @@ static void build_sell(b200_handle* h, edge_partition& ep, const RT* w, sell_lay
     CUDA_TRY(cudaMemsetAsync(f8.data(), 0, n + 8, s));
     CUDA_TRY(cudaMemsetAsync(hist.data(), 0, sizeof(unsigned long long) * nb, s));
     sell_row_starts_kernel<<<sgrid(static_cast<size_t>(nr)), kBT, 0, s>>>(off, nr, f8.data());
-    sell_cell_starts_kernel<<<sgrid(n), kBT, 0, s>>>(idx, ne, B, f8.data());
+    sell_cell_starts_kernel<<<sgrid(n), kBT, 0, s>>>(idx, ne, B, cell_max, f8.data());
     sell_classify_kernel<<<sgrid(n), kBT, static_cast<size_t>(nb) * 4, s>>>(f8.data(), idx, ne, B, nb,
                                                                             c8.data(), hist.data());
     const char* env = std::getenv("B200_BAND_HOT_MIN");
@@ -558,7 +570,7 @@ static void build_sell(b200_handle* h, edge_partition& ep, const RT* w, sell_lay
   dbuf<uint64_t> k0(np, s), k1(np, s);
   dbuf<unsigned long long> total(1, s);
   CUDA_TRY(cudaMemsetAsync(total.data(), 0, 8, s));
-  sell_cell_records_kernel<<<sgrid(n), kBT, 0, s>>>(m8.data(), pid.data(), idx, ne, B, ce0.data(),
+  sell_cell_records_kernel<<<sgrid(n), kBT, 0, s>>>(m8.data(), pid.data(), idx, ne, B, cell_max, ce0.data(),
                                                     k0.data(), v0.data(), total.data());
   CUDA_TRY(cudaGetLastError());
   CUDA_TRY(cudaStreamSynchronize(s));
@@ -589,7 +601,7 @@ static void build_sell(b200_handle* h, edge_partition& ep, const RT* w, sell_lay
   L.p1_slices = S1;
   L.p1_sbase.alloc(static_cast<size_t>(S1) + 1, s);
   sell_p1_groups_kernel<<<sgrid(static_cast<size_t>(S1)), kBT, 0, s>>>(keys, d_bstart.data(),
-                                                                      d_slice_first.data(), nb, S1,
+                                                                      d_slice_first.data(), nb, S1, cell_max,
                                                                       L.p1_sbase.data());
   CUDA_TRY(cudaGetLastError());
   exclusive_scan<uint32_t, uint32_t>(L.p1_sbase.data(), L.p1_sbase.data(), static_cast<size_t>(S1), s, true);
@@ -603,7 +615,7 @@ static void build_sell(b200_handle* h, edge_partition& ep, const RT* w, sell_lay
   L.p1_slot.alloc(static_cast<size_t>(S1) * 32, s);
   sell_p1_fill_kernel<RT><<<sgrid(static_cast<size_t>(S1) * 32), kBT, 0, s>>>(
     keys, vals, ce0.data(), d_bstart.data(), d_slice_first.data(), nb, S1, L.p1_sbase.data(), idx, w, B,
-    L.p1_idx.data(), w ? reinterpret_cast<RT*>(L.p1_w.data()) : nullptr, L.p1_slot.data(),
+    cell_max, L.p1_idx.data(), w ? reinterpret_cast<RT*>(L.p1_w.data()) : nullptr, L.p1_slot.data(),
     band_major ? inv.data() : nullptr);
   CUDA_TRY(cudaGetLastError());
   // tasks and units
@@ -617,8 +629,11 @@ static void build_sell(b200_handle* h, edge_partition& ep, const RT* w, sell_lay
     CUDA_TRY(cudaStreamSynchronize(s));
     std::vector<int64_t> task_first(static_cast<size_t>(nb) + 1);
     task_first[0] = 0;
+    // small graphs: at least ~4 tasks for every warp of the grid
+    const int64_t q1 = std::max<int64_t>(4, std::min<int64_t>(kSellQ1, static_cast<int64_t>(p1_groups) /
+                                                                 (int64_t{h->sm_count} * 32 * 4)));
     for (int k = 0; k < nb; ++k)
-      task_first[k + 1] = task_first[k] + div_up(static_cast<int64_t>(gfirst[k + 1] - gfirst[k]), kSellQ1);
+      task_first[k + 1] = task_first[k] + div_up(static_cast<int64_t>(gfirst[k + 1] - gfirst[k]), q1);
     const int64_t T1 = task_first[nb];
     B200_EXPECTS(T1 > 0 && T1 < (int64_t{1} << 31), kUnknownError, "sell layout: no phase-1 tasks");
     dbuf<int64_t> d_task_first(static_cast<size_t>(nb) + 1, s);
@@ -627,11 +642,11 @@ static void build_sell(b200_handle* h, edge_partition& ep, const RT* w, sell_lay
     L.p1_tasks.alloc(static_cast<size_t>(T1), s);
     L.p1_num_tasks = T1;
     sell_p1_tasks_kernel<<<sgrid(static_cast<size_t>(T1)), kBT, 0, s>>>(
-      d_task_first.data(), d_slice_first.data(), nb, L.p1_sbase.data(), T1, L.p1_tasks.data());
+      d_task_first.data(), d_slice_first.data(), nb, L.p1_sbase.data(), T1, q1, L.p1_tasks.data());
     CUDA_TRY(cudaGetLastError());
     // units of consecutive tasks of one band, in band order; sizes follow guided self-scheduling
     const int nctas = h->sm_count;
-    const int64_t kUnitMin = T1 >= 64 * int64_t{nctas} ? 32 : 4, kUnitMax = 1024;
+    const int64_t kUnitMin = 32, kUnitMax = 1024;
     std::vector<band_group> units;
     int band = 0;
     for (int64_t k = 0; k < T1;) {

@@ -34,7 +34,8 @@
 namespace b200 {
 
 constexpr int kSellG        = 4;      // 16-bit indices per lane and load in phase 1
-constexpr int kSellCellMax  = 512;    // cells are cut at CSC positions that are multiples of this
+constexpr int kSellCellMax  = 512;    // largest cell (cells are cut at CSC positions that are multiples of the
+                                      // build's cell_max: 512 for large graphs, 128 otherwise; sell.cu)
 constexpr int kSellMinCell  = 2;      // cells with fewer edges stay direct gathers
 constexpr int kSellLong     = 128;    // reduced rows with more entries are chunked
 constexpr int kSellWindow   = 1024;   // rows per sort window of phase 2
@@ -43,7 +44,7 @@ constexpr int kSell2Threads = 256;
 #define B200_SELL2_MIN_CTAS 4
 #endif
 constexpr int kSell2MinCtas = B200_SELL2_MIN_CTAS;   // CTAs per SM the phase-2 kernel is compiled for
-constexpr int kSellQ1       = 32;     // phase-1 task quantum: load groups (of 32 * kSellG indices)
+constexpr int kSellQ1       = 32;     // largest phase-1 task quantum: load groups (of 32 * kSellG indices)
 constexpr int kSellQ2       = 96;     // largest phase-2 task quantum: cost units (32 entries or 1/2 slice);
                                       // a task then has < 64 slices (sell_rows_kernel relies on it)
 
