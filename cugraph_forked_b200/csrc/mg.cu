@@ -472,9 +472,11 @@ struct mg_engine {
         CUDA_TRY(cudaMemcpyAsync(x_minor.data() + dis[j], from, row_counts[j] * sizeof(RT),
                                  cudaMemcpyDefault, s));
       }
-    } else {
+    } else if (R > 1) {
       allgatherv(s, h->row, R, h->row_rank, x_local, x_minor.data(), row_counts, sizeof(RT));
     }
+    // a 1 x C grid: the minor range IS the local vertex range, the kernels read x_local itself
+    const RT* xm = R == 1 ? x_local : x_minor.data();
     mark(1);
     const bool time_it = timed < 256;
     if (time_it) {
@@ -487,7 +489,7 @@ struct mg_engine {
     }
     if (fused) {
       RT* part = p2p ? part_local(buf) : partial[0].data();
-      partition_spmv_run(parts[0], x_minor.data(), part, state.data());
+      partition_spmv_run(parts[0], xm, part, state.data());
       if (time_it) {
         CUDA_TRY(cudaEventRecord(ev_time[2 * timed + 1], s));
         ++timed;
@@ -519,7 +521,7 @@ struct mg_engine {
       return;
     }
     for (int i = 0; i < C; ++i) {
-      partition_spmv_run(parts[i], x_minor.data(), partial[i].data(), state.data());
+      partition_spmv_run(parts[i], xm, partial[i].data(), state.data());
       if (C == 1) break;
       CUDA_TRY(cudaEventRecord(ev_part[i], s));
       CUDA_TRY(cudaStreamWaitEvent(h->comm_stream, ev_part[i], 0));

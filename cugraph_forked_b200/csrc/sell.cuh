@@ -188,12 +188,18 @@ __global__ void __launch_bounds__(kBandThreads, 1) sell_band_kernel(const __grid
   RT* band = reinterpret_cast<RT*>(sell_smem);
   __shared__ int s_next;
   __shared__ int s_unit;
+  __shared__ __align__(8) uint64_t s_bar;   // completion of the band's bulk copies
 
   const int tid = threadIdx.x, lane = tid & 31;
   if (blockIdx.x == 0 && tid == 0) *P.queue_next = 0;
   if (P.state && P.state->done) return;
   const RT* x = P.x;
   if (tid < static_cast<int>(16 / sizeof(RT))) band[G::entries + tid] = RT(0);   // the pad entry
+  if (tid == 0) {
+    mbar_init(&s_bar, 1);
+    fence_mbar_init();
+  }
+  uint32_t bar_parity = 0;
 
   int cur_band = -1;
   for (;;) {
@@ -210,12 +216,25 @@ __global__ void __launch_bounds__(kBandThreads, 1) sell_band_kernel(const __grid
       const int n         = static_cast<int>(left < G::entries ? left : G::entries);
       const RT* src       = x + first;
       if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
-        constexpr int per = 16 / sizeof(RT);
-        const int nv      = n / per;
-        const int4* s4    = reinterpret_cast<const int4*>(src);
-        int4* d4          = reinterpret_cast<int4*>(band);
-        for (int i = tid; i < nv; i += kBandThreads) d4[i] = __ldg(s4 + i);
+        // the band comes in by bulk async copies (TMA 1D, SASS UBLKCP): one elected thread issues
+        // them, the copy engine fills shared memory without a load instruction per 16 bytes, and
+        // everybody waits on the mbarrier.  The generic-proxy reads of the previous band were
+        // ordered by the __syncthreads above; the proxy fence orders them before these writes.
+        constexpr int per     = 16 / sizeof(RT);
+        const int nv          = n / per;                   // whole 16-byte units
+        const uint32_t bytes  = static_cast<uint32_t>(nv) * 16u;
+        if (tid == 0 && bytes) {
+          fence_proxy_async();
+          mbar_arrive_expect_tx(&s_bar, bytes);
+          const uint64_t pol = policy_evict_last();        // other CTAs load the same band
+          constexpr uint32_t kChunk = 32768;
+          for (uint32_t o = 0; o < bytes; o += kChunk)
+            bulk_g2s(reinterpret_cast<char*>(band) + o, reinterpret_cast<const char*>(src) + o,
+                     bytes - o < kChunk ? bytes - o : kChunk, &s_bar, pol);
+        }
         for (int i = nv * per + tid; i < n; i += kBandThreads) band[i] = src[i];
+        if (bytes) mbar_wait(&s_bar, bar_parity);
+        if (bytes) bar_parity ^= 1u;
       } else {
         for (int i = tid; i < n; i += kBandThreads) band[i] = src[i];
       }
