@@ -256,7 +256,9 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
   sell = nullptr;
   if (tiled && !ep->offsets64 && env_int("B200_BANDED", kBandedDefault) != 0 &&
       env_int("B200_LAYOUT", 2) == 2) {
-    sell_layout* sl = sell_get<RT>(h, *ep, weights);
+    // partitions of a multi-GPU graph are only ever run with the raw epilogue into a buffer the
+    // caller clears (partition_spmv_run): their all-empty row slices are not stored
+    sell_layout* sl = sell_get<RT>(h, *ep, weights, g->multi_gpu);
     if (sl && sl->enabled) {
       sell = sl;
       pval.alloc(static_cast<size_t>(sl->num_partials) + 1, s, 8);
@@ -1169,11 +1171,15 @@ void partition_spmv_run(partition_spmv* p, const void* x, void* y, const iter_st
   if (p->value_type == B200_FLOAT32) {
     if (p->lf.ep->num_rows == 0) return;
     epi_raw<float> epi{static_cast<float*>(y), 1.0f, 0.0f};
+    if (p->lf.sell && p->lf.sell->skips_empty_rows)
+      CUDA_TRY(cudaMemsetAsync(y, 0, static_cast<size_t>(p->lf.ep->num_rows) * sizeof(float), p->lf.h->stream));
     p->lf.spmv(static_cast<const float*>(x), epi, state, false);
     p->lf.tail(epi, const_cast<iter_state*>(state), 0.0, 0, false, false);
   } else {
     if (p->ld.ep->num_rows == 0) return;
     epi_raw<double> epi{static_cast<double*>(y), 1.0, 0.0};
+    if (p->ld.sell && p->ld.sell->skips_empty_rows)
+      CUDA_TRY(cudaMemsetAsync(y, 0, static_cast<size_t>(p->ld.ep->num_rows) * sizeof(double), p->ld.h->stream));
     p->ld.spmv(static_cast<const double*>(x), epi, state, false);
     p->ld.tail(epi, const_cast<iter_state*>(state), 0.0, 0, false, false);
   }

@@ -387,6 +387,21 @@ __global__ void __launch_bounds__(256) sell_window_sort_kernel(const int32_t* ro
   }
 }
 
+// skip_empty layouts: a row slice is kept when its first (longest) row has entries
+__global__ void sell_keep_flags_kernel(const int32_t* vlen, int64_t nslices, uint32_t* keep)
+{
+  for (int64_t j = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; j < nslices;
+       j += int64_t(gridDim.x) * blockDim.x)
+    keep[j] = vlen[j * 32] > 0 ? 1u : 0u;
+}
+__global__ void sell_keep_map_kernel(const int32_t* vlen, const uint32_t* pos, int64_t nslices,
+                                     int32_t* rmap)
+{
+  for (int64_t j = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; j < nslices;
+       j += int64_t(gridDim.x) * blockDim.x)
+    if (vlen[j * 32] > 0) rmap[pos[j]] = static_cast<int32_t>(j);
+}
+
 __global__ void sell_gather_lengths_kernel(const int32_t* roff, const int32_t* ids, int64_t n, int32_t* out)
 {
   for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n;
@@ -397,8 +412,8 @@ __global__ void sell_gather_lengths_kernel(const int32_t* roff, const int32_t* i
 // length of every phase-2 slice: chunk slices = longest chunk in the slice, row slices = the
 // length of the first (longest) row
 __global__ void sell_p2_lengths_kernel(const int32_t* chunk_len, int64_t num_chunks,
-                                       int64_t chunk_slices, const int32_t* vlen, int64_t nslices,
-                                       uint32_t* slen)
+                                       int64_t chunk_slices, const int32_t* vlen,
+                                       const int32_t* rmap, int64_t nslices, uint32_t* slen)
 {
   for (int64_t s = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; s < nslices;
        s += int64_t(gridDim.x) * blockDim.x) {
@@ -410,7 +425,8 @@ __global__ void sell_p2_lengths_kernel(const int32_t* chunk_len, int64_t num_chu
       }
       slen[s] = static_cast<uint32_t>(m);
     } else {
-      slen[s] = static_cast<uint32_t>(vlen[(s - chunk_slices) * 32]);
+      const int64_t j = rmap ? rmap[s - chunk_slices] : s - chunk_slices;
+      slen[s] = static_cast<uint32_t>(vlen[j * 32]);
     }
   }
 }
@@ -418,7 +434,7 @@ __global__ void sell_p2_lengths_kernel(const int32_t* chunk_len, int64_t num_chu
 // one warp per slice: lane l copies the entries of its row (or chunk) of the reduced CSC
 template <typename RT>
 __global__ void sell_p2_fill_kernel(const int32_t* roff, const int32_t* ridx, const RT* rw,
-                                    const int32_t* vrow, const int32_t* chunk_row,
+                                    const int32_t* vrow, const int32_t* rmap, const int32_t* chunk_row,
                                     const int32_t* chunk_off, const int32_t* chunk_len,
                                     int64_t num_chunks, int64_t chunk_slices, int64_t nslices,
                                     const uint32_t* sbase, int32_t dummy, int32_t x_split,
@@ -434,7 +450,8 @@ __global__ void sell_p2_fill_kernel(const int32_t* roff, const int32_t* ridx, co
       const int64_t c = s * 32 + lane;
       if (c < num_chunks) { first = int64_t(roff[chunk_row[c]]) + chunk_off[c]; len = chunk_len[c]; }
     } else {
-      row = vrow[(s - chunk_slices) * 32 + lane];
+      const int64_t j = rmap ? rmap[s - chunk_slices] : s - chunk_slices;
+      row = vrow[j * 32 + lane];
       if (row >= 0) { first = roff[row]; len = roff[row + 1] - roff[row]; }
     }
     out_row[s * 32 + lane] = row;
@@ -484,7 +501,7 @@ __global__ void sell_gather_u32_kernel(const uint32_t* src, const int64_t* at, i
 }  // namespace
 
 template <typename RT>
-static void build_sell(b200_handle* h, edge_partition& ep, const RT* w, sell_layout& L)
+static void build_sell(b200_handle* h, edge_partition& ep, const RT* w, sell_layout& L, bool skip_empty)
 {
   using G = sell_geom<RT>;
   cudaStream_t s   = h->stream;
@@ -706,7 +723,28 @@ static void build_sell(b200_handle* h, edge_partition& ep, const RT* w, sell_lay
     }
   }
   const int64_t num_chunks = static_cast<int64_t>(chunk_row.size());
-  const int64_t CS = div_up(num_chunks, 32), RS = windows * (kSellWindow / 32), S2 = CS + RS;
+  // skip_empty (multi-GPU partial sums: the caller clears the output): slices whose rows all
+  // have no entry are left out - most rows of a 2D partition have no edge in its column block
+  int64_t RS = windows * (kSellWindow / 32);
+  dbuf<int32_t> rmap;
+  L.skips_empty_rows = false;
+  if (skip_empty) {
+    dbuf<uint32_t> keep(static_cast<size_t>(RS) + 1, s);
+    sell_keep_flags_kernel<<<sgrid(static_cast<size_t>(RS)), kBT, 0, s>>>(vlen.data(), RS, keep.data());
+    CUDA_TRY(cudaGetLastError());
+    exclusive_scan<uint32_t, uint32_t>(keep.data(), keep.data(), static_cast<size_t>(RS), s, true);
+    uint32_t kept = 0;
+    CUDA_TRY(cudaMemcpyAsync(&kept, keep.data() + RS, 4, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    rmap.alloc(std::max<size_t>(kept, 1), s);
+    sell_keep_map_kernel<<<sgrid(static_cast<size_t>(RS)), kBT, 0, s>>>(vlen.data(), keep.data(), RS, rmap.data());
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaStreamSynchronize(s));
+    RS = kept;
+    L.skips_empty_rows = true;
+  }
+  const int32_t* rmap_p = skip_empty ? rmap.data() : nullptr;
+  const int64_t CS = div_up(num_chunks, 32), S2 = CS + RS;
   B200_EXPECTS(S2 < (int64_t{1} << 31) - 1, kUnknownError, "sell layout: too many phase-2 slices");
   L.num_long_rows   = n_long;
   L.num_chunks      = num_chunks;
@@ -726,7 +764,7 @@ static void build_sell(b200_handle* h, edge_partition& ep, const RT* w, sell_lay
                            cudaMemcpyHostToDevice, s));
   L.p2_sbase.alloc(static_cast<size_t>(S2) + 1, s);
   sell_p2_lengths_kernel<<<sgrid(static_cast<size_t>(S2)), kBT, 0, s>>>(d_clen.data(), num_chunks, CS,
-                                                                       vlen.data(), S2, L.p2_sbase.data());
+                                                                       vlen.data(), rmap_p, S2, L.p2_sbase.data());
   CUDA_TRY(cudaGetLastError());
   exclusive_scan<uint32_t, uint32_t>(L.p2_sbase.data(), L.p2_sbase.data(), static_cast<size_t>(S2), s, true);
   uint32_t p2_rows = 0;
@@ -738,7 +776,7 @@ static void build_sell(b200_handle* h, edge_partition& ep, const RT* w, sell_lay
   L.p2_row.alloc(static_cast<size_t>(S2) * 32, s);
   const int32_t dummy = static_cast<int32_t>(L.x_split + n_part);   // pval[n_part] stays zero
   sell_p2_fill_kernel<RT><<<sgrid(static_cast<size_t>(S2) * 32), kBT, 0, s>>>(
-    roff.data(), ridx.data(), w ? rw.data() : nullptr, vrow.data(), d_crow.data(), d_coff.data(),
+    roff.data(), ridx.data(), w ? rw.data() : nullptr, vrow.data(), rmap_p, d_crow.data(), d_coff.data(),
     d_clen.data(), num_chunks, CS, S2, L.p2_sbase.data(), dummy, L.x_split,
     band_major ? inv.data() : nullptr, L.p2_idx.data(),
     w ? reinterpret_cast<RT*>(L.p2_w.data()) : nullptr, L.p2_row.data());
@@ -771,18 +809,18 @@ static void build_sell(b200_handle* h, edge_partition& ep, const RT* w, sell_lay
 }
 
 template <typename RT>
-sell_layout* sell_get(b200_handle* h, edge_partition& ep, const RT* weights)
+sell_layout* sell_get(b200_handle* h, edge_partition& ep, const RT* weights, bool skip_empty)
 {
   const int slot = sizeof(RT) == 4 ? 0 : 1;
   if (!ep.sell[slot]) {
     auto L = std::make_shared<sell_layout>();
-    build_sell<RT>(h, ep, weights, *L);
+    build_sell<RT>(h, ep, weights, *L, skip_empty);
     ep.sell[slot] = L;
   }
   return ep.sell[slot].get();
 }
 
-template sell_layout* sell_get<float>(b200_handle*, edge_partition&, const float*);
-template sell_layout* sell_get<double>(b200_handle*, edge_partition&, const double*);
+template sell_layout* sell_get<float>(b200_handle*, edge_partition&, const float*, bool);
+template sell_layout* sell_get<double>(b200_handle*, edge_partition&, const double*, bool);
 
 }  // namespace b200

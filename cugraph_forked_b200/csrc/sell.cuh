@@ -69,6 +69,7 @@ struct sell_layout {
   int32_t x_split{0};              // phase-2 indices >= x_split refer to partial (index - x_split)
   int64_t num_partials{0};         // pre-reduced cells; pval has one more (zero) entry
   int64_t num_banded_edges{0};
+  bool skips_empty_rows{false};    // rows of all-empty slices are not stored: the caller clears the output
   bool band_major_slots{false};    // partial slots follow the sorted cell order (else row-major)
   // phase 1
   int64_t p1_slices{0};
@@ -430,6 +431,6 @@ __global__ void __launch_bounds__(kSell2Threads, kSell2MinCtas) sell_rows_kernel
 
 // builds (or returns the cached) layout for value width sizeof(RT); sell.cu
 template <typename RT>
-sell_layout* sell_get(b200_handle* h, edge_partition& ep, const RT* weights);
+sell_layout* sell_get(b200_handle* h, edge_partition& ep, const RT* weights, bool skip_empty = false);
 
 }  // namespace b200
