@@ -173,6 +173,67 @@ __global__ void __launch_bounds__(kVT) mg_pagerank_update_kernel(
   store_partials(dang, diff, partials, scratch);
 }
 
+// The same update with the column reduction fused in (peer-memory exchange): the row's sum is
+// the sum of the NSRC copies of this rank's partial-sum slice - its own and NSRC - 1 read over
+// NVLink (ld.cv: never a stale line) - added in column-rank order; 16-byte loads and stores.
+template <typename RT, int NSRC>
+__global__ void __launch_bounds__(kVT) mg_pagerank_update_fused_kernel(
+  RT* pr, const RT* const* srcs, const RT* scale, const RT* pers, RT* x, size_t n,
+  const iter_state* st, RT alpha, RT one_minus_alpha, RT num_vertices, double* partials)
+{
+  __shared__ double scratch[32];
+  constexpr int V = 16 / sizeof(RT);
+  double dang = 0.0, diff = 0.0;
+  if (!st->done) {
+    const RT* s[NSRC];
+#pragma unroll
+    for (int j = 0; j < NSRC; ++j) s[j] = srcs[j];
+    const RT dangling  = static_cast<RT>(st->a);
+    const RT base      = dangling * alpha + one_minus_alpha;
+    const RT unvarying = pers ? RT(0) : base / num_vertices;
+    auto one = [&](RT sum, RT old, RT sc, RT pv, RT& newpr, RT& newx) {
+      RT v = sum + unvarying;
+      if (pers) v += base * pv;
+      diff += fabs(static_cast<double>(v) - static_cast<double>(old));
+      newpr = v;
+      if (sc < RT(0)) { dang += static_cast<double>(v); newx = RT(0); }
+      else newx = v * sc;
+    };
+    const size_t nv = n / V;
+    for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < nv;
+         i += size_t(gridDim.x) * blockDim.x) {
+      alignas(16) RT acc[V], old[V], sc[V], pv[V], np[V], nx[V];
+#pragma unroll
+      for (int k = 0; k < V; ++k) { acc[k] = RT(0); pv[k] = RT(0); }
+#pragma unroll
+      for (int j = 0; j < NSRC; ++j) {
+        const int4 q = __ldcv(reinterpret_cast<const int4*>(s[j]) + i);
+        const RT* qv = reinterpret_cast<const RT*>(&q);
+#pragma unroll
+        for (int k = 0; k < V; ++k) acc[k] += qv[k];
+      }
+      *reinterpret_cast<int4*>(old) = __ldcs(reinterpret_cast<const int4*>(pr) + i);
+      *reinterpret_cast<int4*>(sc)  = __ldcs(reinterpret_cast<const int4*>(scale) + i);
+      if (pers) *reinterpret_cast<int4*>(pv) = __ldcs(reinterpret_cast<const int4*>(pers) + i);
+#pragma unroll
+      for (int k = 0; k < V; ++k) one(acc[k], old[k], sc[k], pv[k], np[k], nx[k]);
+      *(reinterpret_cast<int4*>(pr) + i) = *reinterpret_cast<const int4*>(np);
+      *(reinterpret_cast<int4*>(x) + i)  = *reinterpret_cast<const int4*>(nx);
+    }
+    for (size_t i = nv * V + blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
+         i += size_t(gridDim.x) * blockDim.x) {
+      RT a = RT(0);
+#pragma unroll
+      for (int j = 0; j < NSRC; ++j) a += __ldcv(s[j] + i);
+      RT np1, nx1;
+      one(a, pr[i], scale[i], pers ? pers[i] : RT(0), np1, nx1);
+      pr[i] = np1;
+      x[i]  = nx1;
+    }
+  }
+  store_partials(dang, diff, partials, scratch);
+}
+
 // Katz (katz_centrality_impl.cuh:104-148): new = alpha * sum + beta; a = sum of squares
 template <typename RT>
 __global__ void __launch_bounds__(kVT) mg_katz_update_kernel(const RT* old_c, RT* new_c,
@@ -274,6 +335,8 @@ struct mg_engine {
   // peer-memory exchange (mg_peer.cuh): partial sums and the gathered vector go through an
   // IPC-mapped heap, double-buffered
   bool p2p{false};
+  bool fuse_reduce{false};          // the driver's update kernel sums the C copies itself
+  int last_buf{0};                  // the heap buffer the last SpMV wrote
   peer_heap* heap{nullptr};
   size_t off_part[2]{0, 0}, off_x[2]{0, 0};
   int buf{0};
@@ -367,11 +430,11 @@ struct mg_engine {
   int timed{0};
   // B200_MG_TRACE=1: per-phase device times of the first iterations, printed by rank 0
   bool trace{false};
-  std::vector<cudaEvent_t> ev_trace;  // 5 per iteration: start, gathered, kernels, reduced, end
+  std::vector<cudaEvent_t> ev_trace;  // 6 per iteration: start, gathered, kernels, reduced, updated, end
   void mark(int k)
   {
-    if (!trace || ev_trace.size() >= 5 * 64 + 5) return;
-    if (k == 0 && ev_trace.size() % 5 != 0) return;
+    if (!trace || ev_trace.size() >= 6 * 64 + 6) return;
+    if (k == 0 && ev_trace.size() % 6 != 0) return;
     cudaEvent_t e;
     cudaEventCreate(&e);
     cudaEventRecord(e, h->stream);
@@ -380,20 +443,20 @@ struct mg_engine {
   void print_trace()
   {
     if (!trace || (h->rank != 0 && env_int("B200_MG_TRACE", 0) < 2)) return;
-    size_t iters = ev_trace.size() / 5;
+    size_t iters = ev_trace.size() / 6;
     if (iters == 0) return;
-    double acc[4] = {0, 0, 0, 0};
+    double acc[5] = {0, 0, 0, 0, 0};
     for (size_t i = 0; i < iters; ++i)
-      for (int k = 0; k < 4; ++k) {
+      for (int k = 0; k < 5; ++k) {
         float ms = 0.f;
-        cudaEventElapsedTime(&ms, ev_trace[5 * i + k], ev_trace[5 * i + k + 1]);
+        cudaEventElapsedTime(&ms, ev_trace[6 * i + k], ev_trace[6 * i + k + 1]);
         acc[k] += ms;
       }
     fprintf(stderr,
             "[b200 mg trace] rank %d: %zu iterations: allgather %.1f us, partition kernels %.1f us, "
-            "reduce tail %.1f us, vertex pass + allreduce %.1f us\n",
+            "reduce tail %.1f us, vertex pass %.1f us, scalars %.1f us\n",
             h->rank, iters, 1e3 * acc[0] / iters, 1e3 * acc[1] / iters, 1e3 * acc[2] / iters,
-            1e3 * acc[3] / iters);
+            1e3 * acc[3] / iters, 1e3 * acc[4] / iters);
   }
 
   mg_engine(b200_handle* h_, b200_graph* g_) : h(h_), g(g_)
@@ -499,6 +562,12 @@ struct mg_engine {
         // every column peer has written its partial sums: sum the C copies of this rank's slice
         // (C - 1 of them over NVLink) in column-rank order
         peer_barrier(true);
+        last_buf = buf;
+        if (fuse_reduce) {
+          buf ^= 1;
+          mark(3);
+          return;
+        }
         const size_t n     = static_cast<size_t>(g->fused_slice);
         const unsigned grd = static_cast<unsigned>(std::min<size_t>((n / (16 / sizeof(RT)) + 255) / 256 + 1,
                                                                     size_t(h->sm_count) * 8));
@@ -553,6 +622,7 @@ struct mg_engine {
                       bool deferred = false)
   {
     cudaStream_t s = h->stream;
+    if (iteration > 0) mark(4);
     if (p2p) {
       const uint64_t epoch = ++heap->epoch_scal;
       const int par        = static_cast<int>(epoch & 1);
@@ -563,7 +633,7 @@ struct mg_engine {
         threshold, iteration, check ? 1 : 0, which, heap->d_error);
       CUDA_TRY(cudaGetLastError());
       launches += 1;
-      if (iteration > 0) mark(4);
+      if (iteration > 0) mark(5);
       return;
     }
     mg_fold_kernel<<<1, 256, 0, s>>>(partials.data(), static_cast<int>(vg), state.data(), scal.data());
@@ -588,7 +658,7 @@ struct mg_engine {
       pending_join = true;
     }
     launches += 2;
-    if (iteration > 0) mark(4);
+    if (iteration > 0) mark(5);
   }
   void join_scalars()
   {
@@ -754,6 +824,8 @@ static void pagerank_mg_t(b200_handle* h, b200_graph* g, const b200_pagerank_par
   CUDA_TRY(cudaGetLastError());
   E.reduce_scalars(0.0, 0, false, 1);
 
+  // peer-memory exchange: the update kernel adds the C copies of the partial sums itself
+  E.fuse_reduce = E.p2p && (E.C == 2 || E.C == 4 || E.C == 8) && env_int("B200_MG_FUSE_UPDATE", 1) != 0;
   const int check_every = std::max(1, env_int("B200_CHECK_EVERY", 8));
   scoped_timer timer(s);
   const auto host_t0 = std::chrono::steady_clock::now();
@@ -761,10 +833,23 @@ static void pagerank_mg_t(b200_handle* h, b200_graph* g, const b200_pagerank_par
   for (int64_t it = 0; it < cap; ++it) {
     E.spmv(x.data());
     E.join_scalars();  // the dangling mass and the stop flag of the previous iteration
-    mg_pagerank_update_kernel<RT><<<E.vg, kVT, 0, s>>>(
-      pr.data(), E.result(), scale.data(), personalized ? pers.data() : nullptr, x.data(), n,
-      E.state.data(), alpha, static_cast<RT>(1.0 - p->alpha), static_cast<RT>(g->num_vertices),
-      E.partials.data());
+    if (E.fuse_reduce) {
+      auto go = [&](auto tag) {
+        constexpr int NS = decltype(tag)::value;
+        mg_pagerank_update_fused_kernel<RT, NS><<<E.vg, kVT, 0, s>>>(
+          pr.data(), E.d_srcs[E.last_buf].data(), scale.data(), personalized ? pers.data() : nullptr,
+          x.data(), n, E.state.data(), alpha, static_cast<RT>(1.0 - p->alpha),
+          static_cast<RT>(g->num_vertices), E.partials.data());
+      };
+      if (E.C == 2) go(std::integral_constant<int, 2>{});
+      else if (E.C == 4) go(std::integral_constant<int, 4>{});
+      else go(std::integral_constant<int, 8>{});
+    } else {
+      mg_pagerank_update_kernel<RT><<<E.vg, kVT, 0, s>>>(
+        pr.data(), E.result(), scale.data(), personalized ? pers.data() : nullptr, x.data(), n,
+        E.state.data(), alpha, static_cast<RT>(1.0 - p->alpha), static_cast<RT>(g->num_vertices),
+        E.partials.data());
+    }
     CUDA_TRY(cudaGetLastError());
     ++E.launches;
     E.reduce_scalars(static_cast<double>(epsilon), it + 1, !fixed, 3, true);
