@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(kVT) mg_pagerank_update_kernel(
 // NVLink (ld.cv: never a stale line) - added in column-rank order; 16-byte loads and stores.
 template <typename RT, int NSRC>
 __global__ void __launch_bounds__(kVT) mg_pagerank_update_fused_kernel(
-  RT* pr, const RT* const* srcs, const RT* scale, const RT* pers, RT* x, size_t n,
+  RT* pr, const RT* const* srcs, const RT* scale, const RT* pers, RT* x, RT* x2, size_t n,
   const iter_state* st, RT alpha, RT one_minus_alpha, RT num_vertices, double* partials)
 {
   __shared__ double scratch[32];
@@ -219,6 +219,10 @@ __global__ void __launch_bounds__(kVT) mg_pagerank_update_fused_kernel(
       for (int k = 0; k < V; ++k) one(acc[k], old[k], sc[k], pv[k], np[k], nx[k]);
       *(reinterpret_cast<int4*>(pr) + i) = *reinterpret_cast<const int4*>(np);
       *(reinterpret_cast<int4*>(x) + i)  = *reinterpret_cast<const int4*>(nx);
+      if (x2) {   // the rank's own piece of the minor-range copy (may be 4/8-byte aligned only)
+#pragma unroll
+        for (int k = 0; k < V; ++k) x2[i * V + k] = nx[k];
+      }
     }
     for (size_t i = nv * V + blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
          i += size_t(gridDim.x) * blockDim.x) {
@@ -229,6 +233,7 @@ __global__ void __launch_bounds__(kVT) mg_pagerank_update_fused_kernel(
       one(a, pr[i], scale[i], pers ? pers[i] : RT(0), np1, nx1);
       pr[i] = np1;
       x[i]  = nx1;
+      if (x2) x2[i] = nx1;
     }
   }
   store_partials(dang, diff, partials, scratch);
@@ -345,6 +350,15 @@ struct mg_engine {
   dbuf<double*> d_val_slots[2];
   dbuf<uint64_t*> d_flag_slots;
   RT* part_local(int b) const { return heap->at<RT>(h->rank, off_part[b]); }
+  // where the next gathered vector goes when the driver publishes it itself: the heap buffer the
+  // next spmv() exchanges, and this rank's piece of the minor-range copy
+  RT* x_pub() const { return heap->at<RT>(h->rank, off_x[buf]); }
+  RT* x_own()
+  {
+    size_t d = 0;
+    for (int j = 0; j < h->row_rank; ++j) d += row_counts[j];
+    return x_minor.data() + d;
+  }
   void peer_barrier(bool col)
   {
     const uint64_t epoch = col ? ++heap->epoch_col : ++heap->epoch_row;
@@ -527,10 +541,17 @@ struct mg_engine {
       std::vector<size_t> dis(R + 1, 0);
       for (int j = 0; j < R; ++j) dis[j + 1] = dis[j] + row_counts[j];
       RT* mine = heap->at<RT>(h->rank, off_x[buf]);
-      if (nloc) CUDA_TRY(cudaMemcpyAsync(mine, x_local, nloc * sizeof(RT), cudaMemcpyDeviceToDevice, s));
-      peer_barrier(false);
+      // published: the driver's update kernel wrote this slice into the heap (and into the local
+      // minor-range copy) itself, and the scalar exchange that followed it was a barrier over
+      // all ranks - nothing to copy locally, nothing to wait for
+      const bool published = x_local == mine;
+      if (!published) {
+        if (nloc) CUDA_TRY(cudaMemcpyAsync(mine, x_local, nloc * sizeof(RT), cudaMemcpyDeviceToDevice, s));
+        peer_barrier(false);
+      }
       for (int j = 0; j < R; ++j) {
         if (!row_counts[j]) continue;
+        if (j == h->row_rank && published) continue;
         const RT* from = j == h->row_rank ? x_local : heap->at<RT>((h->rank / R) * R + j, off_x[buf]);
         CUDA_TRY(cudaMemcpyAsync(x_minor.data() + dis[j], from, row_counts[j] * sizeof(RT),
                                  cudaMemcpyDefault, s));
@@ -830,15 +851,20 @@ static void pagerank_mg_t(b200_handle* h, b200_graph* g, const b200_pagerank_par
   scoped_timer timer(s);
   const auto host_t0 = std::chrono::steady_clock::now();
   iter_state hs{};
+  const bool publish = E.fuse_reduce && E.R > 1 && env_int("B200_MG_PUBLISH_X", 1) != 0;
+  const RT* x_cur    = x.data();
   for (int64_t it = 0; it < cap; ++it) {
-    E.spmv(x.data());
+    E.spmv(x_cur);
     E.join_scalars();  // the dangling mass and the stop flag of the previous iteration
+    RT* x_out = publish ? E.x_pub() : x.data();
+    RT* x_two = publish ? E.x_own() : nullptr;
+    x_cur     = x_out;
     if (E.fuse_reduce) {
       auto go = [&](auto tag) {
         constexpr int NS = decltype(tag)::value;
         mg_pagerank_update_fused_kernel<RT, NS><<<E.vg, kVT, 0, s>>>(
           pr.data(), E.d_srcs[E.last_buf].data(), scale.data(), personalized ? pers.data() : nullptr,
-          x.data(), n, E.state.data(), alpha, static_cast<RT>(1.0 - p->alpha),
+          x_out, x_two, n, E.state.data(), alpha, static_cast<RT>(1.0 - p->alpha),
           static_cast<RT>(g->num_vertices), E.partials.data());
       };
       if (E.C == 2) go(std::integral_constant<int, 2>{});
