@@ -53,6 +53,10 @@ class GraphView(ctypes.Structure):
         ("major_last", ctypes.c_int64),
         ("minor_first", ctypes.c_int64),
         ("minor_last", ctypes.c_int64),
+        ("dcs_offsets", ctypes.c_void_p),
+        ("dcs_nzd_vertices", ctypes.c_void_p),
+        ("dcs_nzd_count", ctypes.c_int64),
+        ("major_hypersparse_first", ctypes.c_int64),
     ]
 
 

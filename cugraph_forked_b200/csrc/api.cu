@@ -233,6 +233,13 @@ static void fill_view(const b200_graph* g, int part, b200_graph_view_t* v)
   v->major_last         = ep.major_first + ep.num_rows;
   v->minor_first        = ep.minor_first;
   v->minor_last         = ep.minor_first + ep.num_minors;
+  v->major_hypersparse_first = -1;
+  if (ep.hypersparse_first >= 0) {
+    v->dcs_offsets             = ep.dcs_offsets.data();
+    v->dcs_nzd_vertices        = ep.dcs_nzd_vertices.data();
+    v->dcs_nzd_count           = ep.dcs_nzd_count;
+    v->major_hypersparse_first = ep.major_first + ep.hypersparse_first;
+  }
   if (g->multi_gpu && part < static_cast<int>(g->partition_segment_offsets.size())) {
     auto const& seg = g->partition_segment_offsets[part];
     v->num_segments = static_cast<int32_t>(seg.size()) - 1;

@@ -205,6 +205,11 @@ struct edge_partition {
   // ([0] 4-byte, [1] 8-byte values), built on first use by the pull launcher (banded.cu)
   std::shared_ptr<banded_layout> banded[2];
   std::shared_ptr<sell_layout> sell[2];
+  // DCSC form of the hypersparse segment (multi-GPU partitions, graph_mg.cu step 8b)
+  dbuf<char> dcs_offsets;          // int32 / int64 like `offsets`
+  dbuf<int32_t> dcs_nzd_vertices;  // global internal ids
+  int64_t dcs_nzd_count{0};
+  int64_t hypersparse_first{-1};   // local row index of the segment's first row, -1 if none
 };
 
 }  // namespace b200

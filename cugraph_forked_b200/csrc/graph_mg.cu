@@ -204,6 +204,31 @@ __global__ void fused_offsets_kernel(const unsigned long long* row_start, const 
   }
 }
 
+// DCSC (compress_hypersparse_offsets, structure_utils.cuh:109-159): nz[r - hs] = 1 when row r of
+// the hypersparse segment has edges; after the scan of nz, the non-empty rows are listed and the
+// compressed offsets written
+template <typename ET>
+__global__ void dcs_flags_kernel(const ET* offsets, int64_t hs, int64_t n_rows, uint32_t* nz)
+{
+  for (int64_t r = hs + blockIdx.x * int64_t(blockDim.x) + threadIdx.x; r < n_rows;
+       r += int64_t(gridDim.x) * blockDim.x)
+    nz[r - hs] = offsets[r + 1] > offsets[r] ? 1u : 0u;
+}
+template <typename ET>
+__global__ void dcs_fill_kernel(const ET* offsets, const uint32_t* pos, int64_t hs, int64_t n_rows,
+                                int64_t major_first, ET* dcs_offsets, int32_t* dcs_nzd)
+{
+  for (int64_t r = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; r <= n_rows;
+       r += int64_t(gridDim.x) * blockDim.x) {
+    if (r <= hs) dcs_offsets[r] = offsets[r];   // rows before the segment + the segment's start
+    if (r < n_rows && r >= hs && offsets[r + 1] > offsets[r]) {
+      const uint32_t k       = pos[r - hs];
+      dcs_nzd[k]             = static_cast<int32_t>(major_first + r);
+      dcs_offsets[hs + k + 1] = offsets[r + 1];
+    }
+  }
+}
+
 __global__ void add_u64_to_double_kernel(const unsigned long long* in, size_t n, double* out)
 {
   for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n;
@@ -607,6 +632,42 @@ static void create_mg_t(b200_handle* h, const VT* src, const VT* dst, const void
     std::vector<int64_t> seg(all_meta.begin() + owner * (nseg + 1),
                              all_meta.begin() + owner * (nseg + 1) + nseg);
     g->partition_segment_offsets[i] = seg;
+    // 8b. DCSC form of the hypersparse segment, as the reference holds it (views and parity
+    //     tests; the kernels' layout is built from the uncompressed offsets)
+    ep.hypersparse_first = -1;
+    if (nseg == 6) {
+      const int64_t hs = seg[3];
+      const int64_t nh = ep.num_rows - hs;
+      ep.hypersparse_first = hs;
+      dbuf<uint32_t> nz(static_cast<size_t>(nh) + 1, s);
+      uint32_t cnt = 0;
+      if (nh > 0) {
+        if (ep.offsets64)
+          dcs_flags_kernel<int64_t><<<grid_for(static_cast<size_t>(nh), 4), kThreads, 0, s>>>(
+            reinterpret_cast<const int64_t*>(ep.offsets.data()), hs, ep.num_rows, nz.data());
+        else
+          dcs_flags_kernel<int32_t><<<grid_for(static_cast<size_t>(nh), 4), kThreads, 0, s>>>(
+            reinterpret_cast<const int32_t*>(ep.offsets.data()), hs, ep.num_rows, nz.data());
+        CUDA_TRY(cudaGetLastError());
+        exclusive_scan<uint32_t, uint32_t>(nz.data(), nz.data(), static_cast<size_t>(nh), s, true);
+        CUDA_TRY(cudaMemcpyAsync(&cnt, nz.data() + nh, 4, cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(cudaStreamSynchronize(s));
+      }
+      ep.dcs_nzd_count = cnt;
+      const size_t esz = ep.offsets64 ? 8 : 4;
+      ep.dcs_offsets.alloc((static_cast<size_t>(hs) + cnt + 1) * esz, s, 64);
+      ep.dcs_nzd_vertices.alloc(std::max<size_t>(cnt, 1), s);
+      if (ep.offsets64)
+        dcs_fill_kernel<int64_t><<<grid_for(nr + 1, 4), kThreads, 0, s>>>(
+          reinterpret_cast<const int64_t*>(ep.offsets.data()), nz.data(), hs, ep.num_rows, ep.major_first,
+          reinterpret_cast<int64_t*>(ep.dcs_offsets.data()), ep.dcs_nzd_vertices.data());
+      else
+        dcs_fill_kernel<int32_t><<<grid_for(nr + 1, 4), kThreads, 0, s>>>(
+          reinterpret_cast<const int32_t*>(ep.offsets.data()), nz.data(), hs, ep.num_rows, ep.major_first,
+          reinterpret_cast<int32_t*>(ep.dcs_offsets.data()), ep.dcs_nzd_vertices.data());
+      CUDA_TRY(cudaGetLastError());
+      CUDA_TRY(cudaStreamSynchronize(s));   // nz is freed at the end of this scope
+    }
     ep.has_segments     = true;
     ep.generic_schedule = true;
     ep.seg[0] = 0; ep.seg[1] = seg[1]; ep.seg[2] = seg[2]; ep.seg[3] = seg[nseg - 2];

@@ -203,6 +203,17 @@ class Graph:
         return None if not v.weights else self._copy(v.weights, self._part_edges(partition),
                                                      _TD[v.weight_type])
 
+    def dcs(self, partition: int):
+        """(dcs_offsets, dcs_nzd_vertices, major_hypersparse_first) of a multi-GPU edge partition,
+        or None when it has no hypersparse segment (compress_hypersparse_offsets)."""
+        v = self.view(partition)
+        if v.major_hypersparse_first < 0:
+            return None
+        hs = v.major_hypersparse_first - v.major_first
+        return (self._copy(v.dcs_offsets, hs + v.dcs_nzd_count + 1, _TD[v.edge_type]),
+                self._copy(v.dcs_nzd_vertices, v.dcs_nzd_count, torch.int32),
+                int(v.major_hypersparse_first))
+
     def renumber_map(self) -> torch.Tensor:
         v = self.view()
         return self._copy(v.renumber_map, v.local_vertex_last - v.local_vertex_first,

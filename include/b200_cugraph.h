@@ -85,6 +85,19 @@ typedef struct b200_graph_view {
   /* ranges of this edge partition (graph_view.hpp:181-212); [0, V) on a single GPU.  `indices`
    * hold minor OFFSETS (global minor id - minor_first), the form the kernel gathers with. */
   int64_t major_first, major_last, minor_first, minor_last;
+  /* DCSC form of the hypersparse segment of a multi-GPU edge partition
+   * (compress_hypersparse_offsets, cpp/src/structure/detail/structure_utils.cuh:109-159;
+   * edge_partition_device_view_t::dcs_nzd_vertices, edge_partition_device_view.cuh:159-351):
+   * majors at or after major_hypersparse_first keep an offset only when they have edges.
+   * dcs_offsets = offsets[0 .. hs] ++ offsets[r + 1] of every non-empty row r >= hs
+   * (hs = major_hypersparse_first - major_first), dcs_nzd_vertices = those majors (global
+   * internal ids).  NULL / 0 / -1 when the partition has no hypersparse segment (single GPU,
+   * col_comm_size < 2).  `offsets` above stays the uncompressed array the kernels' layout is
+   * built from. */
+  const void* dcs_offsets;        /* edge_type [hs + dcs_nzd_count + 1]                          */
+  const void* dcs_nzd_vertices;   /* int32     [dcs_nzd_count]                                   */
+  int64_t dcs_nzd_count;
+  int64_t major_hypersparse_first; /* -1 if none                                                  */
 } b200_graph_view_t;
 
 /* Single-GPU graph from a COO edge list (external ids).  vertices may be NULL (vertex set =

@@ -67,6 +67,18 @@ def check_graph(g, oracle, rank, weighted):
         if weighted:
             w = g.weights(i).cpu().numpy()
             assert np.array_equal(w, want["weights"]), f"weights of partition {i} differ"
+        # DCSC form of the hypersparse segment (compress_hypersparse_offsets,
+        # structure_utils.cuh:109-159): present exactly when the oracle says so, bit-exact
+        dcs_want = go.compress_hypersparse(want["offsets"], want["major_first"],
+                                           [int(x) for x in want["segment_offsets"]])
+        dcs = g.dcs(i)
+        assert (dcs is None) == (dcs_want is None), f"DCSC presence of partition {i} differs"
+        if dcs is not None:
+            assert np.array_equal(dcs[0].cpu().numpy().astype(np.int64), dcs_want[0]), \
+                f"dcs offsets of partition {i} differ"
+            assert np.array_equal(dcs[1].cpu().numpy().astype(np.int64), dcs_want[1]), \
+                f"dcs_nzd_vertices of partition {i} differ"
+            assert dcs[2] == want["major_first"] + int(want["segment_offsets"][3])
 
 
 def run(scale: int, edge_factor: int, dtype, weighted: bool, handle, rank, world, verbose=True):
