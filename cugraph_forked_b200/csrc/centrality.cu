@@ -254,7 +254,9 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
   // opt-in fused rectangle keeps the single-phase kernel
   const bool is_fused = !g->fused.empty() && ep == &g->fused[0];
   sell = nullptr;
-  if (tiled && !ep->offsets64 && env_int("B200_BANDED", kBandedDefault) != 0 &&
+  // the sell layout needs no degree order (its rows are window-sorted by reduced length), so
+  // graphs built with renumber = false (the HITS companions) take it too
+  if (!ep->offsets64 && env_int("B200_BANDED", kBandedDefault) != 0 &&
       env_int("B200_LAYOUT", 2) == 2) {
     // partitions of a multi-GPU graph are only ever run with the raw epilogue into a buffer the
     // caller clears (partition_spmv_run): their all-empty row slices are not stored
@@ -326,8 +328,9 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
     if (g->multi_gpu && h->size > 1) {
       // per-partition launches overlap the previous partition's reduction (NCCL needs SMs of its
       // own: these kernels fill the register file); the fused rectangle overlaps only the deferred
-      // 2-scalar allreduce of the previous iteration
-      sell_ctas1 = std::max(1, sell_ctas1 - std::max(0, env_int("B200_MG_RESERVED_SMS", is_fused ? 4 : 16)));
+      // 2-scalar allreduce of the previous iteration, and nothing at all with the peer-memory
+      // exchange (no NCCL kernel is left in the iteration)
+      sell_ctas1 = std::max(1, sell_ctas1 - std::max(0, env_int("B200_MG_RESERVED_SMS", is_fused ? (env_int("B200_MG_P2P", 1) != 0 ? 0 : 4) : 16)));
     }
     main_ctas = sell_ctas1 * per_sm;   // phase-2 grid: 256-thread CTAs, tasks claimed dynamically
     int64_t want_tail = div_up(std::max<int64_t>(sell->num_long_rows, 1), 32);
@@ -370,23 +373,6 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
 {
   cudaStream_t s = h->stream;
   double* parts  = want_partials ? cta_partials.data() : nullptr;
-  if (!tiled) {
-    auto go = [&](auto et, auto wtag) {
-      using ET            = decltype(et);
-      constexpr bool W    = decltype(wtag)::value;
-      pull_rows_generic_kernel<ET, RT, W, EPI><<<main_ctas, 256, 0, s>>>(
-        reinterpret_cast<const ET*>(ep->offsets.data()), ep->indices.data(), weights, x,
-        ep->num_rows, epi, state, parts, slots);
-    };
-    if (ep->offsets64) {
-      if (weighted) go(int64_t{}, std::true_type{}); else go(int64_t{}, std::false_type{});
-    } else {
-      if (weighted) go(int32_t{}, std::true_type{}); else go(int32_t{}, std::false_type{});
-    }
-    CUDA_TRY(cudaGetLastError());
-    ++launches;
-    return;
-  }
   if (sell) {
     sell_params1<RT> A{};
     A.x          = x;
@@ -430,6 +416,23 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
     ++band_launches;
     if (weighted) sell_rows_kernel<RT, true, EPI><<<main_ctas, kSell2Threads, 0, s>>>(Q, epi);
     else          sell_rows_kernel<RT, false, EPI><<<main_ctas, kSell2Threads, 0, s>>>(Q, epi);
+    CUDA_TRY(cudaGetLastError());
+    ++launches;
+    return;
+  }
+  if (!tiled) {
+    auto go = [&](auto et, auto wtag) {
+      using ET            = decltype(et);
+      constexpr bool W    = decltype(wtag)::value;
+      pull_rows_generic_kernel<ET, RT, W, EPI><<<main_ctas, 256, 0, s>>>(
+        reinterpret_cast<const ET*>(ep->offsets.data()), ep->indices.data(), weights, x,
+        ep->num_rows, epi, state, parts, slots);
+    };
+    if (ep->offsets64) {
+      if (weighted) go(int64_t{}, std::true_type{}); else go(int64_t{}, std::false_type{});
+    } else {
+      if (weighted) go(int32_t{}, std::true_type{}); else go(int32_t{}, std::false_type{});
+    }
     CUDA_TRY(cudaGetLastError());
     ++launches;
     return;

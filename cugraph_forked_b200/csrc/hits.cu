@@ -228,9 +228,16 @@ void hits_sg(b200_handle* h, b200_graph* g, const b200_hits_params_t* p, RT* hub
   int64_t final_iteration_count = cap;
   int converged = 0;
   int64_t spmvs = 0;
+  // the two launchers (layouts, schedules, scratch) are built once, not per iteration
+  struct spmv_guard {
+    partition_spmv* p{nullptr};
+    ~spmv_guard() { if (p) partition_spmv_free(p); }
+  } sa, sh;
+  sa.p = partition_spmv_create(h, pull_auth, 0, vt);
+  sh.p = partition_spmv_create(h, pull_hubs, 0, vt);
   for (int64_t iter = 0; iter < cap; ++iter) {
-    spmv_pull(h, pull_auth, vt, prev, 1.0, 0.0, authorities);   // authorities = A^T hubs
-    spmv_pull(h, pull_hubs, vt, authorities, 1.0, 0.0, curr);   // hubs = A authorities
+    partition_spmv_run(sa.p, prev, authorities, nullptr);   // authorities = A^T hubs
+    partition_spmv_run(sh.p, authorities, curr, nullptr);   // hubs = A authorities
     spmvs += 2;
     ops.normalize_max(curr, n);
     ops.normalize_max(authorities, n);

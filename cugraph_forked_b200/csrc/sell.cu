@@ -515,7 +515,7 @@ static void build_sell(b200_handle* h, edge_partition& ep, const RT* w, sell_lay
   const char* env_min     = std::getenv("B200_BAND_MIN_EDGES");
   const int64_t min_edges = env_min ? std::atoll(env_min) : (int64_t{1} << 16);
   if (ne < std::max<int64_t>(min_edges, 64) || ne >= (int64_t{1} << 31) - 4096 || nb <= 0 ||
-      nb > kSellMaxBands || ep.offsets64 || !ep.has_segments || nr >= (int64_t{1} << 31) - 4096)
+      nb > kSellMaxBands || ep.offsets64 || nr >= (int64_t{1} << 31) - 4096)
     return;
   CUDA_TRY(cudaStreamSynchronize(s));
   const auto t_begin = std::chrono::steady_clock::now();
