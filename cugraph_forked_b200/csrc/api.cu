@@ -35,7 +35,6 @@ static void fill_device_info(b200_handle* h)
   CUDA_TRY(cudaGetDeviceProperties(&prop, h->device));
   h->sm_count          = prop.multiProcessorCount;
   h->l2_bytes          = static_cast<size_t>(prop.l2CacheSize);
-  h->persisting_l2_max = static_cast<size_t>(prop.persistingL2CacheMaxSize);
   // random 4/8-byte gathers dominate: a 32-byte L2 fetch granularity halves the DRAM bytes of a
   // gather that misses (the default fetches 64); B200_L2_FETCH=64|128 restores / widens it
   {

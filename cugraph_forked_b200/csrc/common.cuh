@@ -156,7 +156,6 @@ struct b200_handle {
   int device{0};
   int sm_count{148};
   size_t l2_bytes{0};
-  size_t persisting_l2_max{0};
   // multi-GPU
   ncclComm_t world{nullptr}, row{nullptr}, col{nullptr};
   cudaStream_t comm_stream{nullptr};   // per-partition reductions overlap the next SpMV

@@ -11,8 +11,6 @@
 //
 // b200_debug_ingest_emulate runs the same per-thread bodies over the same tiles on the host (no
 // device), for the CPU test-suite.
-#include <cub/block/block_reduce.cuh>
-#include <cub/block/block_scan.cuh>
 
 #include "ingest.cuh"
 #include "ingest_gpu.cuh"
@@ -50,10 +48,9 @@ __global__ void __launch_bounds__(kTileThreads) ingest_pass1_kernel(
   const chunk_counts c = gp_pass1(buf, tile_base, total, threadIdx.x, o);
   counts[static_cast<size_t>(blockIdx.x) * kTileThreads + threadIdx.x] =
     (c.file_entries << 16) | c.out_entries;
-  using reduce_t = cub::BlockReduce<uint32_t, kTileThreads>;
-  __shared__ typename reduce_t::TempStorage tmp_a, tmp_b;
-  const uint32_t f = reduce_t(tmp_a).Sum(c.file_entries);
-  const uint32_t n = reduce_t(tmp_b).Sum(c.out_entries);
+  __shared__ uint32_t red_scratch[32];
+  const uint32_t f = block_sum<uint32_t>(c.file_entries, red_scratch);
+  const uint32_t n = block_sum<uint32_t>(c.out_entries, red_scratch);
   if (threadIdx.x == 0) {
     tile_file[blockIdx.x] = f;
     tile_out[blockIdx.x]  = n;
@@ -72,10 +69,19 @@ __global__ void __launch_bounds__(kTileThreads) ingest_pass2_kernel(
   stage_tile(dtext, tile_base, buf);
   const uint32_t mine =
     counts[static_cast<size_t>(blockIdx.x) * kTileThreads + threadIdx.x] & 0xffffu;
-  using scan_t = cub::BlockScan<uint32_t, kTileThreads>;
-  __shared__ typename scan_t::TempStorage tmp;
-  uint32_t before = 0;
-  scan_t(tmp).ExclusiveSum(mine, before);
+  // exclusive prefix of `mine` over the block: warp scans by shuffle, warp totals through smem
+  __shared__ uint32_t warp_tot[kTileThreads / 32];
+  uint32_t inc = mine;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) warp_tot[wid] = inc;
+  __syncthreads();
+  uint32_t before = inc - mine;
+  for (int w = 0; w < wid; ++w) before += warp_tot[w];
   if (mine == 0) return;
   gp_pass2(
     buf, tile_base, total, threadIdx.x, o, tile_first[blockIdx.x] + before, out,
