@@ -67,13 +67,13 @@ __device__ __forceinline__ uint64_t policy_evict_normal()
 __device__ __forceinline__ float ld_policy(const float* p, uint64_t policy)
 {
   float v;
-  asm volatile("ld.global.nc.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(v) : "l"(p), "l"(policy));
+  asm volatile("ld.global.nc.L1::evict_last.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(v) : "l"(p), "l"(policy));
   return v;
 }
 __device__ __forceinline__ double ld_policy(const double* p, uint64_t policy)
 {
   double v;
-  asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(p), "l"(policy));
+  asm volatile("ld.global.nc.L1::evict_last.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(p), "l"(policy));
   return v;
 }
 // global -> shared bulk copy; bytes % 16 == 0, both addresses 16-byte aligned
