@@ -173,6 +173,12 @@ struct pull_launcher {
   // round-2 layout (sell.cuh): both phases as sliced-ELL kernels; replaces `banded` when enabled
   sell_layout* sell{nullptr};
   int sell_ctas1{0};             // phase-1 grid (one CTA per SM)
+  int64_t queue_uses{0};         // rotating pool of 8 work-queue counters (sell kernels)
+  // Multi-GPU overlap: the minors [split_lo, split_hi) of x are valid when spmv() is called, the
+  // rest once `split_event` has fired (the peer copies of the gathered vector run on a second
+  // stream).  Phase 1 then runs the bands inside that range first.  Cleared by every spmv().
+  int64_t split_lo{0}, split_hi{0};
+  cudaEvent_t split_event{nullptr};
 
   void init(b200_handle* h_, b200_graph* g, edge_partition* ep_);
 
@@ -266,8 +272,9 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
       pval.alloc(static_cast<size_t>(sl->num_partials) + 1, s, 8);
       // the entry behind the last partial is the zero the padding slots of phase 2 read
       CUDA_TRY(cudaMemsetAsync(pval.data() + sl->num_partials, 0, sizeof(RT), s));
-      band_queue.alloc(4, s);   // [0,1] phase 1, [2,3] phase 2: used alternately
-      CUDA_TRY(cudaMemsetAsync(band_queue.data(), 0, 16, s));
+      band_queue.alloc(8, s);   // rotating pool: launch n uses counter n % 8 and clears (n + 4) % 8
+      CUDA_TRY(cudaMemsetAsync(band_queue.data(), 0, 32, s));
+      queue_uses = 0;
       band_launches = 0;
       CUDA_TRY(cudaFuncSetAttribute(sell_band_kernel<RT, true>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -373,6 +380,10 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
 {
   cudaStream_t s = h->stream;
   double* parts  = want_partials ? cta_partials.data() : nullptr;
+  if (!sell && split_event) {   // layouts without a splittable first phase: just wait
+    CUDA_TRY(cudaStreamWaitEvent(s, split_event, 0));
+    split_event = nullptr;
+  }
   if (sell) {
     sell_params1<RT> A{};
     A.x          = x;
@@ -383,16 +394,40 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
     A.slot       = sell->p1_slot.data();
     A.tasks      = sell->p1_tasks.data();
     A.units      = sell->p1_units.data();
-    A.num_units  = static_cast<int32_t>(sell->p1_num_units);
-    A.queue      = band_queue.data() + (band_launches & 1);
-    A.queue_next = band_queue.data() + ((band_launches + 1) & 1);
     A.num_minors = ep->num_minors;
     A.state      = state;
     const size_t smem = sell_geom<RT>::smem;
-    if (weighted) sell_band_kernel<RT, true><<<sell_ctas1, kBandThreads, smem, s>>>(A);
-    else          sell_band_kernel<RT, false><<<sell_ctas1, kBandThreads, smem, s>>>(A);
-    CUDA_TRY(cudaGetLastError());
-    ++launches;
+    auto phase1 = [&](int64_t u0, int64_t u1) {
+      if (u1 <= u0) return;
+      A.unit_first = static_cast<int32_t>(u0);
+      A.unit_end   = static_cast<int32_t>(u1);
+      A.queue      = band_queue.data() + (queue_uses & 7);
+      A.queue_next = band_queue.data() + ((queue_uses + 4) & 7);
+      ++queue_uses;
+      const int grid = static_cast<int>(std::min<int64_t>(sell_ctas1, u1 - u0));
+      if (weighted) sell_band_kernel<RT, true><<<grid, kBandThreads, smem, s>>>(A);
+      else          sell_band_kernel<RT, false><<<grid, kBandThreads, smem, s>>>(A);
+      CUDA_TRY(cudaGetLastError());
+      ++launches;
+    };
+    const int64_t nu = sell->p1_num_units;
+    if (split_event) {
+      // units are in band order: those whose band lies inside [split_lo, split_hi) first, the
+      // others once the rest of x has arrived
+      const int64_t B = sell->band_entries;
+      auto const& ub  = sell->p1_unit_band;
+      int64_t u0 = 0, u1 = 0;
+      while (u0 < nu && static_cast<int64_t>(ub[u0]) * B < split_lo) ++u0;
+      u1 = u0;
+      while (u1 < nu && (static_cast<int64_t>(ub[u1]) + 1) * B <= split_hi) ++u1;
+      phase1(u0, u1);
+      CUDA_TRY(cudaStreamWaitEvent(s, split_event, 0));
+      phase1(0, u0);
+      phase1(u1, nu);
+      split_event = nullptr;
+    } else {
+      phase1(0, nu);
+    }
     sell_params2<RT> Q{};
     Q.x              = x;
     Q.pval           = pval.data();
@@ -405,8 +440,9 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
     Q.num_chunks     = sell->num_chunks;
     Q.task_first     = sell->p2_task_first.data();
     Q.num_tasks      = static_cast<int32_t>(sell->p2_num_tasks);
-    Q.queue          = band_queue.data() + 2 + (band_launches & 1);
-    Q.queue_next     = band_queue.data() + 2 + ((band_launches + 1) & 1);
+    Q.queue          = band_queue.data() + (queue_uses & 7);
+    Q.queue_next     = band_queue.data() + ((queue_uses + 4) & 7);
+    ++queue_uses;
     Q.chunk_partials = chunk_partials.data();
     Q.cta_partials   = parts;
     Q.slots          = slots;
@@ -1185,6 +1221,15 @@ void partition_spmv_run(partition_spmv* p, const void* x, void* y, const iter_st
       CUDA_TRY(cudaMemsetAsync(y, 0, static_cast<size_t>(p->ld.ep->num_rows) * sizeof(double), p->ld.h->stream));
     p->ld.spmv(static_cast<const double*>(x), epi, state, false);
     p->ld.tail(epi, const_cast<iter_state*>(state), 0.0, 0, false, false);
+  }
+}
+
+void partition_spmv_split(partition_spmv* p, int64_t lo, int64_t hi, cudaEvent_t rest_ready)
+{
+  if (p->value_type == B200_FLOAT32) {
+    p->lf.split_lo = lo; p->lf.split_hi = hi; p->lf.split_event = rest_ready;
+  } else {
+    p->ld.split_lo = lo; p->ld.split_hi = hi; p->ld.split_event = rest_ready;
   }
 }
 

@@ -22,6 +22,9 @@ void hits(b200_handle* h, b200_graph* g, const b200_hits_params_t* p, void* hubs
 struct partition_spmv;
 partition_spmv* partition_spmv_create(b200_handle* h, b200_graph* g, int part, int value_type);
 void partition_spmv_run(partition_spmv* p, const void* x, void* y, const iter_state* state);
+// the next partition_spmv_run may start with the minors [lo, hi) of x; the rest is valid once
+// `rest_ready` has fired (ignored by layouts that cannot split their first phase)
+void partition_spmv_split(partition_spmv* p, int64_t lo, int64_t hi, cudaEvent_t rest_ready);
 int64_t partition_spmv_launches(const partition_spmv* p);
 void partition_spmv_free(partition_spmv* p);
 

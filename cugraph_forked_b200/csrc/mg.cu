@@ -437,6 +437,7 @@ struct mg_engine {
   unsigned vg;
   std::vector<cudaEvent_t> ev_part;
   cudaEvent_t ev_red{};
+  cudaEvent_t ev_iter{}, ev_copied{};
   int64_t launches{0};
   bool fused{false};
   // device-time of the partitions' kernels on the main stream
@@ -527,6 +528,8 @@ struct mg_engine {
     for (auto e : ev_part) cudaEventDestroy(e);
     for (auto e : ev_time) cudaEventDestroy(e);
     if (ev_red) cudaEventDestroy(ev_red);
+    if (ev_iter) cudaEventDestroy(ev_iter);
+    if (ev_copied) cudaEventDestroy(ev_copied);
     if (ev_fold) cudaEventDestroy(ev_fold);
     if (ev_commit) cudaEventDestroy(ev_commit);
   }
@@ -549,12 +552,29 @@ struct mg_engine {
         if (nloc) CUDA_TRY(cudaMemcpyAsync(mine, x_local, nloc * sizeof(RT), cudaMemcpyDeviceToDevice, s));
         peer_barrier(false);
       }
+      // published: the peers' slices are copied on the second stream while phase 1 already runs
+      // the bands of this rank's own slice (the launcher splits its unit list at the slice)
+      const bool overlap = published && env_int("B200_MG_OVERLAP_GATHER", 1) != 0 && h->comm_stream;
+      cudaStream_t cs    = overlap ? h->comm_stream : s;
+      if (overlap) {
+        if (!ev_iter) {
+          CUDA_TRY(cudaEventCreateWithFlags(&ev_iter, cudaEventDisableTiming));
+          CUDA_TRY(cudaEventCreateWithFlags(&ev_copied, cudaEventDisableTiming));
+        }
+        CUDA_TRY(cudaEventRecord(ev_iter, s));          // behind the scalar exchange = the barrier
+        CUDA_TRY(cudaStreamWaitEvent(cs, ev_iter, 0));
+      }
       for (int j = 0; j < R; ++j) {
         if (!row_counts[j]) continue;
         if (j == h->row_rank && published) continue;
         const RT* from = j == h->row_rank ? x_local : heap->at<RT>((h->rank / R) * R + j, off_x[buf]);
         CUDA_TRY(cudaMemcpyAsync(x_minor.data() + dis[j], from, row_counts[j] * sizeof(RT),
-                                 cudaMemcpyDefault, s));
+                                 cudaMemcpyDefault, cs));
+      }
+      if (overlap) {
+        CUDA_TRY(cudaEventRecord(ev_copied, cs));
+        partition_spmv_split(parts[0], static_cast<int64_t>(dis[h->row_rank]),
+                             static_cast<int64_t>(dis[h->row_rank + 1]), ev_copied);
       }
     } else if (R > 1) {
       allgatherv(s, h->row, R, h->row_rank, x_local, x_minor.data(), row_counts, sizeof(RT));

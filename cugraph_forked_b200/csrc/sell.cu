@@ -678,6 +678,8 @@ static void build_sell(b200_handle* h, edge_partition& ep, const RT* w, sell_lay
       k = e;
     }
     L.p1_num_units = static_cast<int64_t>(units.size());
+    L.p1_unit_band.resize(units.size());
+    for (size_t k = 0; k < units.size(); ++k) L.p1_unit_band[k] = units[k].band;
     L.p1_units.alloc(units.size(), s);
     CUDA_TRY(cudaMemcpyAsync(L.p1_units.data(), units.data(), units.size() * sizeof(band_group),
                              cudaMemcpyHostToDevice, s));

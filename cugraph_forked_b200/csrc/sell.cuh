@@ -82,6 +82,7 @@ struct sell_layout {
   dbuf<band_group> p1_units;       // work queue: tasks [task_first, task_end) of one band
   int64_t p1_num_tasks{0};
   int64_t p1_num_units{0};
+  std::vector<int32_t> p1_unit_band;   // host copy: band of every unit (units are in band order)
   // phase 2
   int64_t p2_slices{0};
   int64_t p2_chunk_slices{0};      // slices [0, p2_chunk_slices) hold chunks of long rows
@@ -110,7 +111,8 @@ struct sell_params1 {
   const int32_t* slot;
   const sell_task* tasks;
   const band_group* units;
-  int32_t num_units;
+  int32_t unit_first;   // this launch runs the units [unit_first, unit_end)
+  int32_t unit_end;
   int32_t* queue;
   int32_t* queue_next;
   int64_t num_minors;
@@ -207,8 +209,8 @@ __global__ void __launch_bounds__(kBandThreads, 1) sell_band_kernel(const __grid
     __syncthreads();  // every warp is done with the previous unit
     if (tid == 0) s_unit = atomicAdd(P.queue, 1);
     __syncthreads();
-    const int u = s_unit;
-    if (u >= P.num_units) break;
+    const int u = P.unit_first + s_unit;
+    if (u >= P.unit_end) break;
     const band_group grp = P.units[u];
     if (grp.band != cur_band) {
       cur_band            = grp.band;
