@@ -306,7 +306,8 @@ def run_b200(args, rank, world):
     # (rows of the reduced CSC), timed together by the library; + the small tail kernel
     if os.environ.get("B200_BANDED", "1") == "0":
         path, kernels = "tiled", "pull_tiles_kernel"
-    elif os.environ.get("B200_LAYOUT", "2") != "2":
+    elif os.environ.get("B200_LAYOUT", "1" if (world == 1 and ne < (1 << 25)) else "2") != "2":
+        # the library's own rule: round 1's banded path on single-GPU graphs below 2^25 edges
         path, kernels = "banded-r1", "band_reduce_kernel + pull_tiles_kernel (one SpMV)"
     else:
         path, kernels = "sell-r2", "sell_band_kernel + sell_rows_kernel (one SpMV)"

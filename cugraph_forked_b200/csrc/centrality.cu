@@ -10,6 +10,9 @@
 
 #include <climits>
 
+#include <array>
+#include <atomic>
+
 #include "banded.cuh"
 #include "sell.cuh"
 #include "centrality.cuh"
@@ -262,8 +265,14 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
   sell = nullptr;
   // the sell layout needs no degree order (its rows are window-sorted by reduced length), so
   // graphs built with renumber = false (the HITS companions) take it too
-  if (!ep->offsets64 && env_int("B200_BANDED", kBandedDefault) != 0 &&
-      env_int("B200_LAYOUT", 2) == 2) {
+  // Which layout: round 2's sell layout (2) everywhere except on single-GPU graphs below 2^25
+  // edges, where round 1's banded path (1) is faster (scale 20 f32: 238 vs 199 GTEPS, f64 181 vs
+  // 169; from scale 21 on sell wins: 320 vs 306, scale 22 f64 333 vs 238; profiles/r2_notes.md).
+  // B200_LAYOUT overrides.
+  int layout = env_int("B200_LAYOUT", -1);
+  if (layout < 0)
+    layout = (!g->multi_gpu && tiled && ep->num_edges < (int64_t{1} << 25)) ? 1 : 2;
+  if (!ep->offsets64 && env_int("B200_BANDED", kBandedDefault) != 0 && layout == 2) {
     // partitions of a multi-GPU graph are only ever run with the raw epilogue into a buffer the
     // caller clears (partition_spmv_run): their all-empty row slices are not stored
     sell_layout* sl = sell_get<RT>(h, *ep, weights, g->multi_gpu);
@@ -307,8 +316,10 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
       band_queue.alloc(2, s);
       CUDA_TRY(cudaMemsetAsync(band_queue.data(), 0, 8, s));
       band_launches = 0;
-      static bool configured = false;
-      if (!configured) {
+      // the attribute is per device: one flag per device ordinal (a second handle on another
+      // GPU of the process must opt in as well)
+      static std::array<std::atomic<bool>, 64> configured{};
+      if (!configured[h->device & 63].exchange(true)) {
         CUDA_TRY(cudaFuncSetAttribute(band_reduce_kernel<RT, true>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       band_geom<RT>::entries * static_cast<int>(sizeof(RT))));
@@ -321,7 +332,6 @@ void pull_launcher<RT>::init(b200_handle* h_, b200_graph* g, edge_partition* ep_
         CUDA_TRY(cudaFuncSetAttribute(band_reduce2_kernel<RT, false>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       static_cast<int>(band_geom2<RT>::smem)));
-        configured = true;
       }
     } else {
       banded_tiles = false;
@@ -541,11 +551,10 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
     // the entries phase 2 still gathers from x are spread over millions of sources (5 % hit a
     // 16 K cache): no hub cache, the shared memory goes to L1 instead
     if (banded && env_int("B200_BANDED_HUB", 0) == 0) hub = 0;
-    static bool configured = false;
-    if (!configured) {
+    static std::array<std::atomic<bool>, 64> configured{};   // per device ordinal
+    if (!configured[h->device & 63].exchange(true)) {
       CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     static_cast<int>(SM::total(SM::max_hub))));
-      configured = true;
     }
     // split the cache between the pieces of the minor range (one piece on a single GPU)
     std::vector<int64_t> pieces = kp->minor_piece_offsets;
