@@ -382,6 +382,10 @@ struct mg_engine {
     const size_t pb = (static_cast<size_t>(max_part) * sizeof(RT) + 255) & ~size_t{255};
     const size_t xb = (static_cast<size_t>(max_x) * sizeof(RT) + 255) & ~size_t{255};
     heap        = peer_heap_get(h, 2 * pb + 2 * xb);
+    if (!heap) {   // agreed by all ranks: fall back to the collective exchange
+      p2p = false;
+      return;
+    }
     off_part[0] = kPeerHeader;
     off_part[1] = kPeerHeader + pb;
     off_x[0]    = kPeerHeader + 2 * pb;
@@ -498,7 +502,7 @@ struct mg_engine {
       sum_padded.alloc(static_cast<size_t>(g->fused_slice), s, 8);
       p2p = env_int("B200_MG_P2P", 1) != 0;
       if (p2p) setup_p2p();
-      else partial[0].alloc(static_cast<size_t>(g->fused[0].num_rows), s, 8);
+      if (!p2p) partial[0].alloc(static_cast<size_t>(g->fused[0].num_rows), s, 8);
     } else {
       parts.assign(C, nullptr);
       for (int i = 0; i < C; ++i) parts[i] = partition_spmv_create(h, g, i, vt);

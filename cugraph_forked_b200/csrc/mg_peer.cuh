@@ -74,26 +74,39 @@ inline peer_heap* peer_heap_get(b200_handle* h, size_t want)
   heap->world = h->size;
   heap->rank  = h->rank;
   heap->bytes = ((static_cast<size_t>(need) + kPeerHeader + (size_t{2} << 20) - 1) >> 21) << 21;
-  CUDA_TRY(cudaMalloc(&heap->base, heap->bytes));
-  CUDA_TRY(cudaMemset(heap->base, 0, kPeerHeader));
-  CUDA_TRY(cudaMalloc(reinterpret_cast<void**>(&heap->d_error), sizeof(int)));
-  CUDA_TRY(cudaMemset(heap->d_error, 0, sizeof(int)));
-  CUDA_TRY(cudaDeviceSynchronize());
-  cudaIpcMemHandle_t mine;
-  CUDA_TRY(cudaIpcGetMemHandle(&mine, heap->base));
+  // Every rank runs every collective below whatever happens to its own CUDA calls: a failure
+  // (no IPC between these processes, no peer access) is carried in `ok` and agreed on at the end,
+  // so that all ranks fall back to the NCCL exchange together instead of one of them hanging.
+  int64_t ok = 1;
+  auto soft  = [&](cudaError_t e) { if (e != cudaSuccess) { ok = 0; cudaGetLastError(); } };
+  soft(cudaMalloc(&heap->base, heap->bytes));
+  if (ok) soft(cudaMemset(heap->base, 0, kPeerHeader));
+  soft(cudaMalloc(reinterpret_cast<void**>(&heap->d_error), sizeof(int)));
+  if (heap->d_error) soft(cudaMemset(heap->d_error, 0, sizeof(int)));
+  soft(cudaDeviceSynchronize());
+  cudaIpcMemHandle_t mine{};
+  if (ok) soft(cudaIpcGetMemHandle(&mine, heap->base));
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
-  std::vector<int64_t> words(8);
+  std::vector<int64_t> words(9);
   std::memcpy(words.data(), &mine, 64);
+  words[8] = ok;
   std::vector<int64_t> handles = allgather_host(h, h->world, h->size, words);
+  for (int p = 0; p < h->size; ++p) ok = ok && handles[9 * p + 8];
   heap->peer_base.assign(h->size, nullptr);
-  for (int p = 0; p < h->size; ++p) {
+  for (int p = 0; p < h->size && ok; ++p) {
     if (p == h->rank) { heap->peer_base[p] = heap->base; continue; }
     cudaIpcMemHandle_t theirs;
-    std::memcpy(&theirs, handles.data() + 8 * p, 64);
-    CUDA_TRY(cudaIpcOpenMemHandle(&heap->peer_base[p], theirs, cudaIpcMemLazyEnablePeerAccess));
+    std::memcpy(&theirs, handles.data() + 9 * p, 64);
+    soft(cudaIpcOpenMemHandle(&heap->peer_base[p], theirs, cudaIpcMemLazyEnablePeerAccess));
   }
   // nobody may signal into a heap that is not mapped everywhere yet
-  allgather_host(h, h->world, h->size, {int64_t{1}});
+  for (int64_t v : allgather_host(h, h->world, h->size, {ok})) ok = ok && v;
+  if (!ok) {
+    if (h->rank == 0)
+      fprintf(stderr, "[b200] peer-memory exchange unavailable (CUDA IPC / peer access failed on a "
+                      "rank): the multi-GPU iteration uses the NCCL exchange\n");
+    return nullptr;   // `heap` unmaps and frees what it got
+  }
   h->peer = heap;
   return heap.get();
 }
