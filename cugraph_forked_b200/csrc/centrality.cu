@@ -459,6 +459,14 @@ void pull_launcher<RT>::spmv(const RT* x, EPI const& epi, const iter_state* stat
     Q.state          = state;
     Q.hot_limit      = static_cast<int32_t>(std::min<int64_t>(
       ep->num_minors, (static_cast<int64_t>(env_int("B200_HOT_MB", 40)) << 20) / static_cast<int64_t>(sizeof(RT))));
+    // L2 policy hints + streaming epilogue pay when the gathered vector and the partial sums are
+    // far beyond L2 (scale 26 f64, 1.3 GB: +25 %); up to a few times L2 plain loads are 2-3 %
+    // faster (scale 24 f32, 137 MB: 493 vs 481 GTEPS; scale 24 f64, 302 MB: 370 vs 362;
+    // profiles/r2_notes.md).  B200_SELL_HINTS overrides.
+    {
+      const int64_t ws = (ep->num_minors + sell->num_partials) * static_cast<int64_t>(sizeof(RT));
+      Q.use_hints      = env_int("B200_SELL_HINTS", ws > (int64_t{512} << 20) ? 1 : 0);
+    }
     ++band_launches;
     if (weighted) sell_rows_kernel<RT, true, EPI><<<main_ctas, kSell2Threads, 0, s>>>(Q, epi);
     else          sell_rows_kernel<RT, false, EPI><<<main_ctas, kSell2Threads, 0, s>>>(Q, epi);

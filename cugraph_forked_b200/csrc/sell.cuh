@@ -139,6 +139,7 @@ struct sell_params2 {
   int32_t slots;
   const iter_state* state;
   int32_t hot_limit;   // entries [0, hot_limit) of x are kept in L2 (evict_last), the rest streams
+  int32_t use_hints;   // 0: plain read-only loads and stores (working sets that nearly fit L2)
 };
 
 // ------------------------------------------------------------------------------------------
@@ -321,9 +322,11 @@ __global__ void __launch_bounds__(kSell2Threads, kSell2MinCtas) sell_rows_kernel
   // cold tail streams through, the partial sums (eight rows to a line) are ordinary lines
   const uint64_t pol_hot = policy_evict_last(), pol_cold = policy_evict_first(),
                  pol_part = policy_evict_normal();
+  const bool hints = P.use_hints != 0;   // uniform over the grid
   auto gather = [&](int32_t i) -> RT {
     const bool part = i >= P.x_split;
-    return ld_policy((part ? pv : x) + i, part ? pol_part : (i < P.hot_limit ? pol_hot : pol_cold));
+    const RT* a     = (part ? pv : x) + i;
+    return hints ? ld_policy(a, part ? pol_part : (i < P.hot_limit ? pol_hot : pol_cold)) : __ldg(a);
   };
   for (;;) {
     int ti = 0;
@@ -370,7 +373,7 @@ __global__ void __launch_bounds__(kSell2Threads, kSell2MinCtas) sell_rows_kernel
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
         pre[u] = typename EPI::pre_t{};
-        if (row[u] >= 0) pre[u] = epi.prefetch_stream(row[u]);
+        if (row[u] >= 0) pre[u] = hints ? epi.prefetch_stream(row[u]) : epi.prefetch(row[u]);
         RT v[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -417,7 +420,8 @@ __global__ void __launch_bounds__(kSell2Threads, kSell2MinCtas) sell_rows_kernel
           const int64_t c = static_cast<int64_t>(s_first + k + u) * 32 + lane;
           if ((u == 0 || two) && c < P.num_chunks) P.chunk_partials[c] = static_cast<double>(sum);
         } else if (row[u] >= 0) {
-          epi.finish_stream(row[u], sum, pre[u], acc, P.hot_limit);
+          if (hints) epi.finish_stream(row[u], sum, pre[u], acc, P.hot_limit);
+          else epi.finish(row[u], sum, pre[u], acc);
         }
       }
     }
