@@ -500,7 +500,9 @@ struct mg_engine {
       parts.assign(1, partition_spmv_create(h, g, -1, vt));
       partial.resize(1);
       sum_padded.alloc(static_cast<size_t>(g->fused_slice), s, 8);
-      p2p = env_int("B200_MG_P2P", 1) != 0;
+      // the peer reduction is instantiated for 2, 4 and 8 column peers (the grids of 2 / 4 / 8 /
+      // 16 GPUs); other grids keep the NCCL exchange
+      p2p = env_int("B200_MG_P2P", 1) != 0 && (C == 2 || C == 4 || C == 8);
       if (p2p) setup_p2p();
       if (!p2p) partial[0].alloc(static_cast<size_t>(g->fused[0].num_rows), s, 8);
     } else {
