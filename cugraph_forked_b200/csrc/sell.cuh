@@ -25,7 +25,12 @@
 //            chunks (slices of their own) whose sums the tail kernel combines in a fixed order.
 //
 // The reference has no counterpart (per_v_transform_reduce_incoming_outgoing_e.cuh:194-479 walks
-// the CSC rows directly).  Same sums in another fixed association order; deterministic.
+// the CSC rows directly).  Every row sum is the same sum in another FIXED association order (cells,
+// slices, lanes and chunk order are fixed at build time; only the warp that runs a task is
+// dynamic), so scores are reproducible run to run.  The two iteration scalars (L1 difference,
+// dangling mass) are fp64 sums of per-CTA partials whose composition follows the dynamic task
+// claims: they can differ in the last bit between runs (never seen to change an fp32 result or
+// an iteration count; tests/test_gpu_centrality.py asserts bit-equal repeated runs).
 #pragma once
 
 #include "banded.cuh"
